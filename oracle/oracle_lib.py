@@ -1,0 +1,194 @@
+"""ctypes bindings for oracle/libnaive_oracle.so (our C restatement of the reference CPU math)
+and, when present, oracle/_ref/libref_naive.so (the unmodified reference CPU code compiled by
+oracle/Makefile).  TEST INFRASTRUCTURE ONLY -- see naive_oracle.c header.
+
+All functions take/return contiguous float32 numpy arrays in the reference layout:
+Q,K,V,O,dO,dQ,dK,dV are row-major [N, d]; L/l/m are [N]
+(reference: src/util/naive_attention.h:7-8, :84-87).
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libnaive_oracle.so")
+_REF = os.path.join(_HERE, "_ref", "libref_naive.so")
+
+_fp = C.POINTER(C.c_float)
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+def build(force=False):
+    """Compile the checker (gcc only).  Called by __graft_entry__.build() and lazily by tests."""
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(os.path.join(_HERE, "naive_oracle.c")):
+        subprocess.check_call(["make", "-C", _HERE, "libnaive_oracle.so"], stdout=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF)):
+        subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_LIB)
+    return _lib
+
+
+def ref_available():
+    return os.path.exists(_REF)
+
+
+def ref():
+    """The unmodified reference CPU implementation (oracle/_ref); None if it was never built."""
+    global _ref
+    if _ref is None and os.path.exists(_REF):
+        _ref = C.CDLL(_REF)
+    return _ref
+
+
+def _f(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a, a.ctypes.data_as(_fp)
+
+
+def num_threads():
+    return int(lib().oracle_num_threads())
+
+
+def forward(Q, K, V, scale=0.0, want_L=True):
+    """oracle_forward == naive_forward_pass (src/util/naive_attention.h:7-61); Nq may differ from Nkv."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    Nq, d = Q.shape; Nkv = K.shape[0]
+    O = np.empty((Nq, d), np.float32); L = np.empty((Nq,), np.float32)
+    lib().oracle_forward(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp) if want_L else None,
+                         C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return (O, L) if want_L else O
+
+
+def forward_rows(Q, K, V, rows, scale=0.0):
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    d = Q.shape[1]; Nkv = K.shape[0]
+    O = np.empty((len(rows), d), np.float32); L = np.empty((len(rows),), np.float32)
+    lib().oracle_forward_rows(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp),
+                              rows.ctypes.data_as(_ip), C.c_int(len(rows)), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return O, L
+
+
+def forward_batched(Q, K, V, scale=0.0, nthreads=1):
+    """Q [BH,Nq,d], K,V [BH,Nkv,d]: one reference call per (b,h) slab, optionally on several cores."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    BH, Nq, d = Q.shape; Nkv = K.shape[1]
+    O = np.empty_like(Q); L = np.empty((BH, Nq), np.float32)
+    lib().oracle_forward_batched(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp), C.c_int(BH),
+                                 C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale), C.c_int(nthreads))
+    return O, L
+
+
+def forward_f64(Q, K, V, scale=0.0):
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    Nq, d = Q.shape; Nkv = K.shape[0]
+    O = np.empty((Nq, d), np.float64); L = np.empty((Nq,), np.float64)
+    lib().oracle_forward_f64(q, k, v, O.ctypes.data_as(_dp), L.ctypes.data_as(_dp),
+                             C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return O, L
+
+
+def attention_rowwise(Q, K, V):
+    """oracle_attention_rowwise == naive_attention (src/00_naive_attention/main.cpp:8-38)."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    N, d = Q.shape
+    O = np.empty((N, d), np.float32)
+    lib().oracle_attention_rowwise(q, k, v, O.ctypes.data_as(_fp), C.c_int(N), C.c_int(d))
+    return O
+
+
+def fa1(Q, K, V):
+    """FlashAttention-1 outputs (O, l, m), src/01_flash_attention_v1/flash_attention_kernel.cu:113-128,156-157."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    N, d = Q.shape
+    O = np.empty((N, d), np.float32); l = np.empty((N,), np.float32); m = np.empty((N,), np.float32)
+    lib().oracle_fa1(q, k, v, O.ctypes.data_as(_fp), l.ctypes.data_as(_fp), m.ctypes.data_as(_fp), C.c_int(N), C.c_int(d))
+    return O, l, m
+
+
+def backward_jacobian(Q, K, V, dO, scale):
+    """oracle_backward_jacobian == naive_attention_backward (src/util/naive_attention.h:84-161), O(N^3)."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
+    N, d = Q.shape
+    dQ = np.empty((N, d), np.float32); dK = np.empty((N, d), np.float32); dV = np.empty((N, d), np.float32)
+    lib().oracle_backward_jacobian(q, k, v, None, None, g, dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp),
+                                   dV.ctypes.data_as(_fp), C.c_int(N), C.c_int(d), C.c_float(scale))
+    return dQ, dK, dV
+
+
+def backward(Q, K, V, dO, scale=0.0):
+    """O(N^2 d) restatement (dS = P o (dP - D)), double accumulation; Nq may differ from Nkv."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
+    Nq, d = Q.shape; Nkv = K.shape[0]
+    dQ = np.empty((Nq, d), np.float32); dK = np.empty((Nkv, d), np.float32); dV = np.empty((Nkv, d), np.float32)
+    lib().oracle_backward(q, k, v, g, dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp), dV.ctypes.data_as(_fp),
+                          C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return dQ, dK, dV
+
+
+def ring_step(Q, Kblk, Vblk, O, Lbuf, M, scale, last_step):
+    """In-place carry step, src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:67-139."""
+    Q, q = _f(Q); Kblk, k = _f(Kblk); Vblk, v = _f(Vblk)
+    assert O.dtype == np.float32 and Lbuf.dtype == np.float32 and M.dtype == np.float32
+    Nq, d = Q.shape; Nkv = Kblk.shape[0]
+    lib().oracle_ring_step(q, k, v, O.ctypes.data_as(_fp), Lbuf.ctypes.data_as(_fp), M.ctypes.data_as(_fp),
+                           C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale), C.c_int(1 if last_step else 0))
+
+
+def lse_merge(Oa, La, Ob, Lb):
+    """In place on (Oa, La): merge two normalised partials by log-sum-exp."""
+    Ob, ob = _f(Ob); Lb, lb = _f(Lb)
+    N, d = Oa.shape
+    lib().oracle_lse_merge(Oa.ctypes.data_as(_fp), La.ctypes.data_as(_fp), ob, lb, C.c_int(N), C.c_int(d))
+
+
+def compare_outputs(ref_arr, test_arr, rtol=1e-3, atol=1.0):
+    """Failing-element count under the ring test's rule (src/util/attention_helper.h:174-208)."""
+    a, pa = _f(np.ravel(ref_arr)); b, pb = _f(np.ravel(test_arr))
+    return int(lib().oracle_compare_outputs(pa, pb, C.c_int(a.size), C.c_float(rtol), C.c_float(atol)))
+
+
+# ---- the unmodified reference (oracle/_ref) -------------------------------------------------
+def ref_forward_pass(Q, K, V, scale):
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    N, d = Q.shape
+    O = np.empty((N, d), np.float32); L = np.empty((N,), np.float32)
+    ref().ref_naive_forward_pass(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp), C.c_int(N), C.c_int(d), C.c_float(scale))
+    return O, L
+
+
+def ref_backward(Q, K, V, dO, scale):
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
+    N, d = Q.shape
+    dQ = np.empty((N, d), np.float32); dK = np.empty((N, d), np.float32); dV = np.empty((N, d), np.float32)
+    ref().ref_naive_attention_backward(q, k, v, None, None, g, dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp),
+                                       dV.ctypes.data_as(_fp), C.c_int(N), C.c_int(d), C.c_float(scale))
+    return dQ, dK, dV
+
+
+def ref_attention_rowwise(Q, K, V):
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
+    N, d = Q.shape
+    O = np.empty((N, d), np.float32)
+    ref().ref_naive_attention(q, k, v, O.ctypes.data_as(_fp), C.c_int(N), C.c_int(d))
+    return O
+
+
+def ref_fixture(name, n_elems):
+    """Reference test inputs that depend on glibc rand() (see ref_wrapper.cpp)."""
+    arrs = [np.empty((n_elems,), np.float32) for _ in range(4 if name == "bwd_random" else 3)]
+    fn = getattr(ref(), "ref_fixture_" + name)
+    fn(*[a.ctypes.data_as(_fp) for a in arrs], C.c_int(n_elems))
+    return arrs
