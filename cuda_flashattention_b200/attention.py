@@ -1,0 +1,108 @@
+"""Host-side mirror of the reference's operator interface, on torch CUDA tensors.
+
+Same names, argument meaning and layouts as the reference's C++ wrappers (citations are paths in
+the reference repository); each call goes straight through the C-ABI of libb200attn.so.
+torch is used only for device memory and streams.
+
+    flash_attention_2_forward(Q, K, V, softmax_scale)            -> (O, L)
+        src/02_flash_attention_v2_forward/flash_attention_kernel.cu:300
+    flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale) -> (dQ, dK, dV)
+        src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:249
+    flash_attention(Q, K, V)                                     -> (O, l, m)
+        src/01_flash_attention_v1/main.cu:7
+
+Tensors are [N, d] (one head, the reference's shape) or [B, H, N, d]; fp32 or bf16; contiguous.
+"""
+import torch
+
+from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32
+
+
+def _dtype_code(t):
+    if t.dtype == torch.float32:
+        return B200_DTYPE_F32
+    if t.dtype == torch.bfloat16:
+        return B200_DTYPE_BF16
+    raise TypeError(f"unsupported dtype {t.dtype}: fp32 and bf16 only")
+
+
+def _check_inputs(*ts):
+    dev, dt = ts[0].device, ts[0].dtype
+    for t in ts:
+        if not t.is_cuda:
+            raise ValueError("cuda_flashattention_b200 has no CPU path: tensors must live on a CUDA device")
+        if t.device != dev or t.dtype != dt:
+            raise ValueError("all tensors must share device and dtype")
+        if not t.is_contiguous():
+            raise ValueError("tensors must be contiguous row-major [.., N, d] (the reference layout)")
+
+
+def _bhnd(t):
+    if t.dim() == 2:
+        return 1, 1, t.shape[0], t.shape[1]
+    if t.dim() == 4:
+        return tuple(t.shape)
+    raise ValueError("expected [N, d] or [B, H, N, d]")
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True):
+    _check_inputs(Q, K, V)
+    B, H, Nq, d = _bhnd(Q)
+    Bk, Hk, Nkv, dk = _bhnd(K)
+    if (Bk, Hk, dk) != (B, H, d) or tuple(V.shape) != tuple(K.shape):
+        raise ValueError("Q/K/V shape mismatch")
+    O = torch.empty_like(Q)
+    L = torch.empty(Q.shape[:-1], dtype=torch.float32, device=Q.device)
+    with torch.cuda.device(Q.device):
+        check(lib.b200_fa2_fwd(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(),
+                               B, H, Nq, Nkv, d, float(softmax_scale), _dtype_code(Q), _stream()), "b200_fa2_fwd")
+    return (O, L) if return_lse else O
+
+
+def flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale=0.0):
+    _check_inputs(Q, K, V, O, dO)
+    B, H, Nq, d = _bhnd(Q)
+    _, _, Nkv, _ = _bhnd(K)
+    if L.dtype != torch.float32 or not L.is_contiguous():
+        raise ValueError("L must be contiguous fp32")
+    dQ, dK, dV = torch.empty_like(Q), torch.empty_like(K), torch.empty_like(V)
+    with torch.cuda.device(Q.device):
+        check(lib.b200_fa2_bwd(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(), dO.data_ptr(),
+                               dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), B, H, Nq, Nkv, d, float(softmax_scale),
+                               _dtype_code(Q), None, 0, _stream()), "b200_fa2_bwd")
+    return dQ, dK, dV
+
+
+def flash_attention(Q, K, V):
+    """FlashAttention-1 API: returns (O, l, m) with l = sum exp(s - m), m = rowmax; scale 1/sqrt(d); synchronous."""
+    _check_inputs(Q, K, V)
+    if Q.dim() != 2 or Q.dtype != torch.float32:
+        raise ValueError("flash_attention (FA1 API) takes one fp32 head [N, d]")
+    N, d = Q.shape
+    O = torch.empty_like(Q)
+    l = torch.empty(N, dtype=torch.float32, device=Q.device)
+    m = torch.empty(N, dtype=torch.float32, device=Q.device)
+    with torch.cuda.device(Q.device):
+        check(lib.b200_fa1_fwd_f32(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), l.data_ptr(), m.data_ptr(),
+                                   N, d, _stream()), "b200_fa1_fwd_f32")
+    return O, l, m
+
+
+def lse_merge_(Oa, La, Ob, Lb):
+    """In place on (Oa, La): merge two normalised partials by log-sum-exp."""
+    _check_inputs(Oa, Ob)
+    B, H, N, d = _bhnd(Oa)
+    with torch.cuda.device(Oa.device):
+        check(lib.b200_lse_merge(Oa.data_ptr(), La.data_ptr(), Ob.data_ptr(), Lb.data_ptr(), B, H, N, d,
+                                 _dtype_code(Oa), _stream()), "b200_lse_merge")
+    return Oa, La
+
+
+def uses_tensor_cores(dtype, d, Nq, Nkv, backward=False):
+    code = B200_DTYPE_F32 if dtype == torch.float32 else B200_DTYPE_BF16
+    fn = lib.b200_bwd_uses_tensor_cores if backward else lib.b200_fwd_uses_tensor_cores
+    return bool(fn(code, d, Nq, Nkv))

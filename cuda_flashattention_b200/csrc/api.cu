@@ -1,0 +1,203 @@
+// api.cu -- the extern "C" boundary declared in include/b200attn.h: argument validation, routing
+// between the tcgen05 tensor-core kernels and the generic CUDA-core kernels, scratch arena.
+#include "common.cuh"
+#include <math.h>
+#include <mutex>
+
+namespace b200 {
+
+static thread_local int g_last_cuda_error = 0;
+void set_last_cuda_error(int code) { g_last_cuda_error = code; }
+
+struct Arena { void* ptr = nullptr; size_t bytes = 0; };
+static Arena g_arena[64];
+static std::mutex g_arena_mu;
+
+int arena_get(size_t bytes, void** out)
+{
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return B200_ERR_INVALID_ARGUMENT;
+    std::lock_guard<std::mutex> lk(g_arena_mu);
+    Arena& a = g_arena[dev];
+    if (a.bytes < bytes) {
+        if (a.ptr) { B200_CUDA_TRY(cudaDeviceSynchronize()); B200_CUDA_TRY(cudaFree(a.ptr)); a.ptr = nullptr; a.bytes = 0; }
+        size_t want = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+        B200_CUDA_TRY(cudaMalloc(&a.ptr, want));
+        a.bytes = want;
+    }
+    *out = a.ptr;
+    return B200_OK;
+}
+
+static int g_dev_state[64];   // 0 unknown, 1 ok, -1 wrong arch
+static int g_dev_sms[64];
+int device_check()
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_last_cuda_error((int)e); (void)cudaGetLastError(); return B200_ERR_NO_DEVICE; }
+    if (dev < 0 || dev >= 64) return B200_ERR_INVALID_ARGUMENT;
+    if (g_dev_state[dev] == 0) {
+        int major = 0, sms = 0;
+        e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+        if (e != cudaSuccess) { set_last_cuda_error((int)e); (void)cudaGetLastError(); return B200_ERR_NO_DEVICE; }
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        g_dev_sms[dev] = sms;
+        g_dev_state[dev] = (major == 10) ? 1 : -1;
+    }
+    return g_dev_state[dev] == 1 ? B200_OK : B200_ERR_ARCH;
+}
+int num_sms()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    return g_dev_sms[dev] > 0 ? g_dev_sms[dev] : 148;
+}
+
+static inline bool valid_dtype(int dt) { return dt == B200_DTYPE_BF16 || dt == B200_DTYPE_F32; }
+static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sqrtf((float)d) : s; }
+
+static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
+                    float scale, int dtype, cudaStream_t st)
+{
+    if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
+    if (BH == 0 || Nq == 0) return B200_OK;
+    if (Nkv == 0) return B200_ERR_INVALID_ARGUMENT;            // softmax over an empty set is undefined
+    if (!Q || !K || !V || !O) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    scale = resolve_scale(scale, d);
+    if (tc_fwd_supported(dtype, d, Nq, Nkv)) return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st);
+    return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
+}
+
+static size_t bwd_ws_bytes(int BH, int Nq, int Nkv, int d, int dtype)
+{
+    size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
+    size_t tc = tc_bwd_supported(dtype, d, Nq, Nkv) ? tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype) : 0;
+    return dbytes + tc;
+}
+
+static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                    void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
+                    void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
+    if (BH == 0 || (Nq == 0 && Nkv == 0)) return B200_OK;
+    if (Nq == 0 || Nkv == 0) return B200_ERR_INVALID_ARGUMENT;
+    if (!Q || !K || !V || !O || !L || !dO || !dQ || !dK || !dV) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    scale = resolve_scale(scale, d);
+    const size_t need = bwd_ws_bytes(BH, Nq, Nkv, d, dtype);
+    if (ws == nullptr) B200_TRY(arena_get(need, &ws));
+    else if (ws_bytes < need) return B200_ERR_WORKSPACE;
+    float* D = reinterpret_cast<float*>(ws);
+    const size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
+    B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
+    if (tc_bwd_supported(dtype, d, Nq, Nkv))
+        return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
+                      reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
+    return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+const char* b200_strerror(int s)
+{
+    switch (s) {
+        case B200_OK: return "ok";
+        case B200_ERR_INVALID_ARGUMENT: return "invalid argument";
+        case B200_ERR_UNSUPPORTED_HEAD_DIM: return "unsupported head dimension";
+        case B200_ERR_CUDA: return "CUDA call failed (see b200_last_cuda_error)";
+        case B200_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+        case B200_ERR_ARCH: return "device is not compute capability 10.x (sm_100a kernels only)";
+        case B200_ERR_WORKSPACE: return "workspace too small";
+        case B200_ERR_NCCL: return "NCCL call failed";
+        case B200_ERR_UNSUPPORTED: return "unsupported configuration";
+        default: return "unknown status";
+    }
+}
+int b200_last_cuda_error(void) { return g_last_cuda_error; }
+int b200_version(void) { return 100; }
+
+int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
+int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_bwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
+
+int b200_fa2_fwd_f32(const float* Q, const float* K, const float* V, float* O, float* L, int N, int d, float scale, cudaStream_t st)
+{ return fwd_impl(Q, K, V, O, L, 1, N, N, d, scale, B200_DTYPE_F32, st); }
+
+int b200_fa2_bwd_f32(const float* Q, const float* K, const float* V, const float* O, const float* L, const float* dO,
+                     float* dQ, float* dK, float* dV, int N, int d, float scale, cudaStream_t st)
+{ return bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, 1, N, N, d, scale, B200_DTYPE_F32, nullptr, 0, st); }
+
+int b200_fa1_fwd_f32(const float* Q, const float* K, const float* V, float* O, float* l, float* m, int N, int d, cudaStream_t st)
+{
+    if (N < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
+    if (N == 0) return B200_OK;
+    if (!Q || !K || !V || !O || !l || !m) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    // (l, m) are the un-logged statistics; the generic kernel emits them directly.
+    B200_TRY(simt_fwd(Q, K, V, O, l, m, 1, N, N, d, 1.0f / sqrtf((float)d), B200_DTYPE_F32, 1, st));
+    B200_CUDA_TRY(cudaStreamSynchronize(st));      // reference flash_attention() synchronises (01/main.cu:64)
+    return B200_OK;
+}
+
+int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nq, int Nkv, int d,
+                 float scale, int dtype, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    return fwd_impl(Q, K, V, O, L, B * H, Nq, Nkv, d, scale, dtype, st);
+}
+
+size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
+{
+    if (B <= 0 || H <= 0 || Nq <= 0 || Nkv <= 0 || d <= 0 || !valid_dtype(dtype)) return 0;
+    return bwd_ws_bytes(B * H, Nq, Nkv, d, dtype);
+}
+
+int b200_fa2_bwd(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                 void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
+                 void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    return bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, B * H, Nq, Nkv, d, scale, dtype, ws, ws_bytes, st);
+}
+
+int b200_rowdot(const void* dO, const void* O, float* D, int B, int H, int N, int d, int dtype, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || N < 0 || d <= 0 || !valid_dtype(dtype)) return B200_ERR_INVALID_ARGUMENT;
+    if ((size_t)B * H * N == 0) return B200_OK;
+    if (!dO || !O || !D) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    return rowdot(dO, O, D, (size_t)B * H * N, d, dtype, st);
+}
+
+int b200_lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, int B, int H, int N, int d, int dtype, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || N < 0 || d <= 0 || !valid_dtype(dtype)) return B200_ERR_INVALID_ARGUMENT;
+    if ((size_t)B * H * N == 0) return B200_OK;
+    if (!Oa || !La || !Ob || !Lb) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    return lse_merge(Oa, La, Ob, Lb, (size_t)B * H * N, d, dtype, st);
+}
+
+int b200_release_workspace(void)
+{
+    std::lock_guard<std::mutex> lk(g_arena_mu);
+    for (int i = 0; i < 64; ++i)
+        if (g_arena[i].ptr) {
+            int cur = 0;
+            cudaGetDevice(&cur);
+            cudaSetDevice(i);
+            cudaFree(g_arena[i].ptr);
+            cudaSetDevice(cur);
+            g_arena[i].ptr = nullptr; g_arena[i].bytes = 0;
+        }
+    return B200_OK;
+}
+
+}  // extern "C"

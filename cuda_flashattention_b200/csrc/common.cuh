@@ -1,0 +1,56 @@
+// common.cuh -- internal declarations shared by the translation units of libb200attn.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/b200attn.h"
+
+namespace b200 {
+
+void set_last_cuda_error(int code);
+
+#define B200_CUDA_TRY(call)                                   \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) {                             \
+            ::b200::set_last_cuda_error((int)e__);            \
+            (void)cudaGetLastError();                         \
+            return B200_ERR_CUDA;                             \
+        }                                                     \
+    } while (0)
+
+#define B200_TRY(call)                                        \
+    do {                                                      \
+        int s__ = (call);                                     \
+        if (s__ != B200_OK) return s__;                       \
+    } while (0)
+
+// ---- generic CUDA-core kernels (generic_simt.cu) ------------------------------------------------
+// mode 0: O + LSE (L may be NULL);  mode 1: O + l (into L) + m (into M)   [FA1 API]
+int simt_fwd(const void* Q, const void* K, const void* V, void* O, float* L, float* M, int BH, int Nq, int Nkv, int d,
+             float scale, int dtype, int mode, cudaStream_t st);
+int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtype, cudaStream_t st);
+// dQ may be NULL (skip), or dK and dV both NULL (skip)
+int simt_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
+             void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st);
+int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st);
+
+// ---- tcgen05 tensor-core kernels (fwd_sm100.cu / bwd_sm100.cu) ------------------------------------
+bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv);
+int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
+           float scale, int dtype, cudaStream_t st);
+bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
+size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
+int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
+           void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
+           void* ws, size_t ws_bytes, cudaStream_t st);
+
+// ---- per-device scratch arena (api.cu) ------------------------------------------------------------
+// Grows monotonically; reuse across calls is safe because all users are stream-ordered on the
+// caller's stream and growth synchronises the device before freeing the old block.
+int arena_get(size_t bytes, void** out);
+int device_check();          // B200_OK iff the current device is compute capability 10.x
+int num_sms();
+
+}  // namespace b200

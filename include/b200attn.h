@@ -1,0 +1,158 @@
+/*
+ * b200attn.h -- C-ABI of the B200-native (sm_100a) exact-attention library.
+ *
+ * This is the drop-in boundary for the reference's hot path.  The reference
+ * (terryye/cuda_FlashAttention) has no FFI: its boundary is a set of C++ free functions defined
+ * in .cu files that the drivers #include textually.  Each entry point below names the reference
+ * function it replaces (paths relative to the reference root); compat/ holds source-compat
+ * shims that re-create the reference's C++ signatures on top of this ABI, and INTEGRATION.md
+ * shows the binding a maintainer would add.
+ *
+ * Conventions (same as the reference unless noted):
+ *   - All tensor pointers are DEVICE pointers owned by the caller; nothing is retained.
+ *   - Layout: one head is row-major [N, d] contiguous (row stride d); batched tensors are
+ *     [B, H, N, d] contiguous so every (b,h) slab is one reference call; L / l / m are [B, H, N] fp32.
+ *   - Non-causal, no mask, no dropout, no bias.  `scale` multiplies QK^T; scale == 0 selects
+ *     1/sqrt(d) (reference src/util/naive_attention.h:9).  LSE is the natural log of the sum of
+ *     exp of the SCALED scores.
+ *   - Calls enqueue work on `stream` and return without synchronising (reference wrappers launch
+ *     on the legacy default stream and return; pass stream = 0 for identical behaviour).
+ *   - Every function returns B200_OK (0) or a negative b200_status; nothing aborts or asserts.
+ *     (The reference returns void and drops errors; see b200_strerror.)
+ *   - There is no CPU fallback: without a CUDA device / on a non-sm_100 device the calls fail with
+ *     B200_ERR_NO_DEVICE / B200_ERR_ARCH.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+#ifndef NCCL_H_
+typedef struct ncclComm* ncclComm_t;
+#endif
+
+typedef enum {
+    B200_OK = 0,
+    B200_ERR_INVALID_ARGUMENT = -1,
+    B200_ERR_UNSUPPORTED_HEAD_DIM = -2,
+    B200_ERR_CUDA = -3,          /* a CUDA runtime/driver call failed; b200_last_cuda_error() has the code */
+    B200_ERR_NO_DEVICE = -4,
+    B200_ERR_ARCH = -5,          /* device is not compute capability 10.x */
+    B200_ERR_WORKSPACE = -6,     /* caller-provided workspace too small */
+    B200_ERR_NCCL = -7,
+    B200_ERR_UNSUPPORTED = -8
+} b200_status;
+
+typedef enum {
+    B200_DTYPE_BF16 = 0,         /* bf16 I/O, bf16 tensor-core operands, fp32 accumulation */
+    B200_DTYPE_F32 = 1           /* fp32 I/O (the reference's type), tf32 tensor-core operands, fp32 accumulation */
+} b200_dtype;
+
+B200_API const char* b200_strerror(int status);
+B200_API int b200_last_cuda_error(void);
+B200_API int b200_version(void);
+
+/* Which kernel family a (dtype, d, Nq, Nkv) problem is routed to: 1 = tcgen05 tensor-core path,
+ * 0 = generic CUDA-core path (tiny / odd shapes; still on the GPU). */
+B200_API int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
+B200_API int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
+
+/* ---- reference-signature entry points (one head, fp32) -------------------------------------- */
+
+/* Replaces flash_attention_2_forward(Q,K,V,O,L,seq_len,head_dim,softmax_scale):
+ *   src/02_flash_attention_v2_forward/flash_attention_kernel.cu:300-343 and
+ *   src/03_flash_attention_v2_ring/common/flash_attention_kernel.cu:133-172.   L may be NULL. */
+B200_API int b200_fa2_fwd_f32(const float* Q, const float* K, const float* V, float* O, float* L,
+                     int seq_len, int head_dim, float softmax_scale, cudaStream_t stream);
+
+/* Replaces flash_attention_2_backward(Q,K,V,O,L,dO,dQ,dK,dV,seq_len,head_dim,softmax_scale):
+ *   src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:249-299.
+ * dQ, dK, dV are fully overwritten (the reference memsets dK/dV then accumulates). Scratch for
+ * D = rowsum(dO o O) is taken from an internal per-device arena (stream-ordered). */
+B200_API int b200_fa2_bwd_f32(const float* Q, const float* K, const float* V, const float* O, const float* L,
+                     const float* dO, float* dQ, float* dK, float* dV,
+                     int seq_len, int head_dim, float softmax_scale, cudaStream_t stream);
+
+/* Replaces flash_attention(d_Q,d_K,d_V,d_O,d_l,d_m,N,d,Bc,M): src/01_flash_attention_v1/main.cu:7-70.
+ * Outputs normalised O, l = sum_j exp(s_j - m) and m = rowmax (NOT the LSE); scale fixed at
+ * 1/sqrt(d) (main.cu:60).  The reference synchronises before returning; so does this call. */
+B200_API int b200_fa1_fwd_f32(const float* Q, const float* K, const float* V, float* O, float* l, float* m,
+                     int N, int d, cudaStream_t stream);
+
+/* ---- batched entry points ([B,H,N,d] contiguous) ---------------------------------------------- */
+
+B200_API int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L,
+                 int B, int H, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t stream);
+
+/* Workspace the batched backward needs (D vector and, on the tensor-core path, an fp32 dQ
+ * accumulator).  Pass workspace = NULL to let the library use its internal arena. */
+B200_API size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype);
+
+B200_API int b200_fa2_bwd(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                 void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
+                 void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/* D[b,h,i] = sum_c dO[b,h,i,c] * O[b,h,i,c]   (reference flash_attention_backward_kernel.cu:97-120) */
+B200_API int b200_rowdot(const void* dO, const void* O, float* D, int B, int H, int N, int d, int dtype, cudaStream_t stream);
+
+/* In place on (Oa, La): merge two normalised partial results by log-sum-exp:
+ *   L = log(e^La + e^Lb),  O = e^(La-L) Oa + e^(Lb-L) Ob.
+ * Equivalent to the reference ring kernel's (m, l, O_unnorm) carry,
+ * src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:67-79,109-139. */
+B200_API int b200_lse_merge(void* Oa, float* La, const void* Ob, const float* Lb,
+                   int B, int H, int N, int d, int dtype, cudaStream_t stream);
+
+/* ---- ring attention (sequence sharded over nranks GPUs, one process per GPU) ------------------ */
+
+/* KV block that `rank` attends to at ring step `step`: (rank - step) mod nranks
+ * (reference common/ring_attention_kernel.cu:198).  Pure host function. */
+B200_API int b200_ring_kv_block(int rank, int step, int nranks);
+
+/* Replaces ring_attention_forward(Q_local,K_local,V_local,O_local,L_local,total_seq_len,
+ * local_seq_len,head_dim,softmax_scale,comm,rank,nranks):
+ *   src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:143-239, with
+ *   ring_exchange_kv (src/util/nccl_utils.h:133-142) on an internal side stream.
+ * Batched: local shards are [B,H,N_local,d]; L_local is [B,H,N_local] (LSE).  K_local/V_local are
+ * NOT modified (the reference overwrites them for nranks >= 3).  nranks == 1 needs no communicator. */
+B200_API int b200_ring_fwd(const void* Q_local, const void* K_local, const void* V_local, void* O_local, float* L_local,
+                  int B, int H, int N_local, int d, float scale, int dtype,
+                  ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
+
+/* Ring backward (not in the reference): Q,dO,O,L,dQ stay, (K,V,dK,dV) rotate so that
+ * dK/dV arrive home fully reduced. */
+B200_API int b200_ring_bwd(const void* Q_local, const void* K_local, const void* V_local, const void* O_local,
+                  const float* L_local, const void* dO_local, void* dQ_local, void* dK_local, void* dV_local,
+                  int B, int H, int N_local, int d, float scale, int dtype,
+                  ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
+
+/* NCCL bootstrap without MPI (replaces init_nccl_comm / cleanup_mpi_nccl, src/util/nccl_utils.h:29-103):
+ * rank 0 calls b200_ring_unique_id and ships the 128 bytes to the other ranks by any means
+ * (file, env, torch.distributed store), then every rank calls b200_ring_comm_init. */
+B200_API int b200_ring_unique_id(void* out128);
+B200_API int b200_ring_comm_init(ncclComm_t* comm, const void* id128, int rank, int nranks);
+B200_API int b200_ring_comm_destroy(ncclComm_t comm);
+/* ring_exchange_kv (src/util/nccl_utils.h:133-142): grouped send(next)/recv(prev) of two buffers. */
+B200_API int b200_ring_exchange_kv(const void* send_k, void* recv_k, const void* send_v, void* recv_v, size_t bytes_each,
+                          int next_rank, int prev_rank, ncclComm_t comm, cudaStream_t stream);
+
+/* Frees the library's per-device scratch arena (optional; also released at process exit). */
+B200_API int b200_release_workspace(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

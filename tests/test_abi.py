@@ -1,0 +1,57 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/b200attn.h declares, and fails loudly (never falls back) when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+import cuda_flashattention_b200 as fa
+from conftest import ROOT
+
+
+def _declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "b200attn.h")).read()
+    return sorted(set(re.findall(r"B200_API\s+[\w\s\*]+?\b(b200_\w+)\s*\(", hdr)))
+
+
+def test_header_symbols_exported():
+    names = _declared_symbols()
+    assert len(names) >= 20
+    raw = C.CDLL(fa.LIB_PATH)
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in include/b200attn.h but not exported"
+    assert set(names) == set(fa.EXPORTS), "python binding table out of sync with the header"
+
+
+def test_version_and_strerror():
+    assert fa.lib.b200_version() >= 100
+    assert b"no CPU fallback" in fa.lib.b200_strerror(-4)
+    assert fa.lib.b200_strerror(0) == b"ok"
+
+
+def test_ring_schedule_is_reference_schedule():
+    # kv_block_idx = (rank - step + nranks) % nranks, common/ring_attention_kernel.cu:198
+    for P in (1, 2, 3, 4, 8):
+        for r in range(P):
+            seen = [fa.ring_kv_block(r, s, P) for s in range(P)]
+            assert seen == [(r - s + P) % P for s in range(P)]
+            assert sorted(seen) == list(range(P))          # every block visited exactly once
+
+
+def test_invalid_arguments_rejected_without_device():
+    assert fa.lib.b200_fa2_fwd_f32(None, None, None, None, None, -1, 4, 1.0, None) == -1
+    assert fa.lib.b200_fa2_fwd(None, None, None, None, None, 1, 1, 4, 4, 4, 1.0, 7, None) == -1      # bad dtype
+    assert fa.lib.b200_fa2_fwd_f32(None, None, None, None, None, 0, 4, 1.0, None) == 0                 # empty: no-op
+    assert fa.lib.b200_fa2_bwd_workspace_bytes(1, 1, 128, 128, 64, 0) >= 128 * 4
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    # dummy non-null pointers: the call must stop at the device check, before touching them
+    st = fa.lib.b200_fa2_fwd_f32(8, 8, 8, 8, None, 4, 4, 1.0, None)
+    assert st in (-4, -3), st
+    q = torch.zeros(4, 4)
+    with pytest.raises(ValueError):
+        fa.flash_attention_2_forward(q, q, q)
