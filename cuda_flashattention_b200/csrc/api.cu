@@ -55,6 +55,8 @@ int num_sms()
     return g_dev_sms[dev] > 0 ? g_dev_sms[dev] : 148;
 }
 
+static int g_force_generic = 0;   // test hook: route everything to the CUDA-core kernels (GPU cross-check)
+
 static inline bool valid_dtype(int dt) { return dt == B200_DTYPE_BF16 || dt == B200_DTYPE_F32; }
 static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sqrtf((float)d) : s; }
 
@@ -67,7 +69,7 @@ static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float*
     if (!Q || !K || !V || !O) return B200_ERR_INVALID_ARGUMENT;
     B200_TRY(device_check());
     scale = resolve_scale(scale, d);
-    if (tc_fwd_supported(dtype, d, Nq, Nkv)) return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st);
+    if (!g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv)) return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st);
     return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
 }
 
@@ -94,7 +96,7 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     float* D = reinterpret_cast<float*>(ws);
     const size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
     B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
-    if (tc_bwd_supported(dtype, d, Nq, Nkv))
+    if (!g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv))
         return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
                       reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
     return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
@@ -123,6 +125,7 @@ const char* b200_strerror(int s)
 }
 int b200_last_cuda_error(void) { return g_last_cuda_error; }
 int b200_version(void) { return 100; }
+int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generic = on ? 1 : 0; return old; }
 
 int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
 int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_bwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }

@@ -1,6 +1,367 @@
-// placeholder until the tcgen05 forward lands
+// fwd_sm100.cu -- FlashAttention-2 forward for sm_100a: TMA -> swizzled smem -> tcgen05.mma with
+// accumulators in TMEM, warp-specialised producer / MMA-issuer / softmax roles.
+//
+// Replaces flash_attention_2_forward_kernel (reference
+// src/02_flash_attention_v2_forward/flash_attention_kernel.cu:37-297 and the 32-lane build in
+// src/03_flash_attention_v2_ring/common/flash_attention_kernel.cu:13-130) and its inner step
+// process_kv_block (src/util/attention_helper.h:40-132): S = QK^T, m' = max(m, rowmax),
+// P = e^(S-m'), l = e^(m-m') l + rowsum(P), O = e^(m-m') O + PV, end: O /= l, L = m + log l.
+//
+// One CTA owns NT (1 or 2) query tiles of 128 rows of one (b,h) slab and streams all K/V tiles:
+//   warp 0      TMA producer: Q tiles once, then a STAGES-deep ring of K and V tiles
+//   warp 1      MMA issuer (one thread): S_t = Q_t K_j^T (SS), O_t += P_t V_j (A = P from TMEM)
+//   warp 2      TMEM allocator
+//   warps 4..   one softmax warpgroup per query tile: thread = row; tcgen05.ld the S row,
+//               rowmax / exp2 / rowsum in registers (no shuffles: a thread owns a whole row),
+//               lazy O rescale in TMEM, P back to TMEM (aliasing S), final O/l -> smem -> TMA store.
+// With NT = 2 the two tiles ping-pong: while warpgroup 0 does the softmax of S_0(j) the tensor
+// pipe runs PV_1(j-1) and S_1(j), and vice versa.
+// TMEM map (512 columns): S_t / P_t at 128 t, O_t at 256 + 128 t.
 #include "common.cuh"
+#include "ptx.cuh"
+#include "tmap.h"
+
 namespace b200 {
-bool tc_fwd_supported(int, int, int, int) { return false; }
-int tc_fwd(const void*, const void*, const void*, void*, float*, int, int, int, int, float, int, cudaStream_t) { return B200_ERR_UNSUPPORTED; }
+
+template <typename Elem_, int D_, int NT_, int BC_>
+struct FwdCfg {
+    using Elem = Elem_;
+    static constexpr int EB = sizeof(Elem);
+    static constexpr bool kF32 = (EB == 4);
+    static constexpr int D = D_, NT = NT_, BC = BC_, BR = 128, STAGES = 2;
+    static constexpr int CPB = 128 / EB;                 // elements per 128-byte swizzle row ("box" width)
+    static constexpr int KPER = 32 / EB;                 // K elements per tcgen05.mma (bf16: 16, tf32: 8)
+    static constexpr int BOXES = D / CPB;                // boxes along d in a Q / K / V / O tile
+    static constexpr int Q_BOX = BR * 128, KV_BOX = BC * 128;
+    static constexpr int Q_TILE = BOXES * Q_BOX, KV_TILE = BOXES * KV_BOX;
+    static constexpr int THREADS = 128 + NT * 128;
+    static constexpr int NBARS = NT * 4 + STAGES * 4;
+    static constexpr int SMEM = 1024 + NT * Q_TILE + 2 * STAGES * KV_TILE + NBARS * 8 + 16;
+    static constexpr int PCOLS_PER_CHUNK = kF32 ? 32 : 16;   // TMEM columns written per 32 P values
+    // V is the MN-major B operand of O += P V.  bf16: plain 128B swizzle.  tf32: the hardware only
+    // accepts the 32-byte-atom 128B swizzle for MN-major operands (4-row pattern, SBO = 512).
+    static constexpr uint32_t V_LAYOUT = kF32 ? 1u : 2u;
+    static constexpr uint32_t V_SBO = kF32 ? 512u : 1024u;
+    static_assert(D % CPB == 0 && BC % 32 == 0 && BC <= 128 && D <= 128, "tile shape");
+    static_assert(SMEM <= 227 * 1024, "shared memory budget");
+};
+
+__device__ __forceinline__ uint32_t cvt_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
 }
+
+template <bool F32>
+__device__ __forceinline__ void umma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, bool acc) {
+    if constexpr (F32) umma_tf32_ss(d, a, b, idesc, acc ? 1u : 0u); else umma_f16_ss(d, a, b, idesc, acc ? 1u : 0u);
+}
+template <bool F32>
+__device__ __forceinline__ void umma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, bool acc) {
+    if constexpr (F32) umma_tf32_ts(d, a_tmem, b, idesc, acc ? 1u : 0u); else umma_f16_ts(d, a_tmem, b, idesc, acc ? 1u : 0u);
+}
+
+// Lazy-rescale threshold in log2 units: the running max is only refreshed (and O rescaled) when
+// it would grow by more than this, so stale-max probabilities stay <= 2^8 (exact in the end:
+// O and l carry the same stale max, which cancels in O / l and is added back in the LSE).
+constexpr float kRescaleThreshold = 8.0f;
+
+// One softmax warpgroup (128 threads) serving query tile t.  Thread r owns query row r of the tile.
+template <class C>
+__device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, uint64_t* bar_S, uint64_t* bar_P,
+                                             uint64_t* bar_O, const CUtensorMap* tmO, float* __restrict__ Lout,
+                                             int Nq, int Nkv, int nkv, int q0, int bh, float scale_log2)
+{
+    constexpr int BC = C::BC, D = C::D;
+    const int wg_thread = threadIdx.x & 127;                       // == TMEM lane == row within the tile
+    const int warp_in_wg = (threadIdx.x >> 5) & 3;
+    const uint32_t lane_base = uint32_t(warp_in_wg * 32) << 16;
+    const uint32_t tS = tmem + 128 * t + lane_base;                // S_t and (aliased) P_t
+    const uint32_t tO = tmem + 256 + 128 * t + lane_base;
+    const int tail = Nkv - (nkv - 1) * BC;                         // valid columns in the last K/V tile
+
+    float m = -INFINITY, l = 0.0f;                                 // m in log2 units (already scaled)
+    for (int j = 0; j < nkv; ++j) {
+        mbar_wait(bar_S, j & 1);
+        tc_fence_after();
+        uint32_t s[BC];
+#pragma unroll
+        for (int c = 0; c < BC / 32; ++c) B200_TMEM_LD_32(tS + 32 * c, s + 32 * c);
+        tmem_wait_ld();
+        if (j == nkv - 1 && tail < BC) {
+#pragma unroll
+            for (int i = 0; i < BC; ++i) if (i >= tail) s[i] = 0xff800000u;      // -inf
+        }
+        float mx = __uint_as_float(s[0]);
+#pragma unroll
+        for (int i = 1; i < BC; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+        const float m_new = fmaxf(m, mx * scale_log2);
+        const bool need = (m_new - m) > kRescaleThreshold;
+        float alpha = 1.0f;
+        if (need) { alpha = fast_exp2(m - m_new); m = m_new; }
+        if (j > 0 && __any_sync(0xffffffffu, need)) {
+            // PV_t(j-1) is complete (bar_S(j) was committed after it), PV_t(j) not yet issued: O_t is ours.
+#pragma unroll
+            for (int c = 0; c < D / 32; ++c) {
+                uint32_t o[32];
+                B200_TMEM_LD_32(tO + 32 * c, o);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                B200_TMEM_ST_32(tO + 32 * c, o);
+            }
+        }
+        const float neg_m = -m;
+        float lsum = 0.0f;
+#pragma unroll
+        for (int c = 0; c < BC / 32; ++c) {
+            float p[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                p[i] = fast_exp2(fmaf(__uint_as_float(s[32 * c + i]), scale_log2, neg_m));
+                lsum += p[i];
+            }
+            if constexpr (C::kF32) {
+                uint32_t r[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) r[i] = cvt_tf32(p[i]);
+                B200_TMEM_ST_32(tS + 32 * c, r);
+            } else {
+                uint32_t r[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) r[i] = pack_bf16x2(p[2 * i], p[2 * i + 1]);
+                B200_TMEM_ST_16(tS + 16 * c, r);
+            }
+        }
+        l = l * alpha + lsum;
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_P);
+    }
+
+    // ---- epilogue: O_t / l -> smem (reusing the Q tile, 128B-swizzled) -> TMA store; LSE -> global
+    mbar_wait(bar_O, 0);
+    tc_fence_after();
+    const float inv_l = 1.0f / l;
+    uint8_t* sO = sQ + t * C::Q_TILE;
+    const int r = wg_thread;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        B200_TMEM_LD_32(tO + 32 * c, o);
+        tmem_wait_ld();
+        if constexpr (C::kF32) {
+            // 32 floats = one 128-byte box row: box c, 8 chunks of 16 B
+            uint8_t* rowp = sO + c * C::Q_BOX + r * 128;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                float4 v = make_float4(__uint_as_float(o[4 * q]) * inv_l, __uint_as_float(o[4 * q + 1]) * inv_l,
+                                       __uint_as_float(o[4 * q + 2]) * inv_l, __uint_as_float(o[4 * q + 3]) * inv_l);
+                *reinterpret_cast<float4*>(rowp + ((q ^ (r & 7)) * 16)) = v;
+            }
+        } else {
+            // 32 bf16 = 64 B = 4 chunks: box c/2, chunks (c&1)*4 .. +3
+            uint8_t* rowp = sO + (c >> 1) * C::Q_BOX + r * 128;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint4 v;
+                v.x = pack_bf16x2(__uint_as_float(o[8 * q]) * inv_l, __uint_as_float(o[8 * q + 1]) * inv_l);
+                v.y = pack_bf16x2(__uint_as_float(o[8 * q + 2]) * inv_l, __uint_as_float(o[8 * q + 3]) * inv_l);
+                v.z = pack_bf16x2(__uint_as_float(o[8 * q + 4]) * inv_l, __uint_as_float(o[8 * q + 5]) * inv_l);
+                v.w = pack_bf16x2(__uint_as_float(o[8 * q + 6]) * inv_l, __uint_as_float(o[8 * q + 7]) * inv_l);
+                const int chunk = (c & 1) * 4 + q;
+                *reinterpret_cast<uint4*>(rowp + ((chunk ^ (r & 7)) * 16)) = v;
+            }
+        }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1 + t, 128);
+    if (wg_thread == 0) {
+#pragma unroll
+        for (int b = 0; b < C::BOXES; ++b) tma_store_3d(tmO, sO + b * C::Q_BOX, b * C::CPB, q0 + t * 128, bh);
+        tma_store_commit();
+        tma_store_wait<0>();
+    }
+    const int row = q0 + t * 128 + r;
+    if (Lout != nullptr && row < Nq)
+        Lout[(size_t)bh * Nq + row] = (m + log2f(l)) * 0.6931471805599453f;
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+           const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+           float* __restrict__ Lout, int Nq, int Nkv, float scale_log2)
+{
+    constexpr int NT = C::NT, BC = C::BC, D = C::D, ST = C::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + NT * C::Q_TILE;
+    uint8_t* sV = sK + ST * C::KV_TILE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ST * C::KV_TILE);
+    uint64_t* bar_Q = bars;                 // [NT]  Q tile landed
+    uint64_t* bar_S = bar_Q + NT;           // [NT]  S_t(j) complete in TMEM
+    uint64_t* bar_P = bar_S + NT;           // [NT]  P_t(j) written (128 arrivals)
+    uint64_t* bar_O = bar_P + NT;           // [NT]  last PV of tile t complete
+    uint64_t* bar_Kf = bar_O + NT;          // [ST]
+    uint64_t* bar_Ke = bar_Kf + ST;
+    uint64_t* bar_Vf = bar_Ke + ST;
+    uint64_t* bar_Ve = bar_Vf + ST;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_Ve + ST);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.y;
+    const int q0 = blockIdx.x * (NT * 128);
+    const int ntiles = min(NT, (Nq - q0 + 127) / 128);
+    const int nkv = (Nkv + BC - 1) / BC;
+
+    if (threadIdx.x == 0) {
+        for (int t = 0; t < NT; ++t) { mbar_init(&bar_Q[t], 1); mbar_init(&bar_S[t], 1); mbar_init(&bar_P[t], 128); mbar_init(&bar_O[t], 1); }
+        for (int s = 0; s < ST; ++s) { mbar_init(&bar_Kf[s], 1); mbar_init(&bar_Ke[s], 1); mbar_init(&bar_Vf[s], 1); mbar_init(&bar_Ve[s], 1); }
+        fence_mbar_init();
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
+    }
+    if (warp == 2) { tmem_alloc<512>(tmem_slot); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            for (int t = 0; t < ntiles; ++t) {
+                mbar_expect_tx(&bar_Q[t], C::Q_TILE);
+                for (int b = 0; b < C::BOXES; ++b)
+                    tma_load_3d(sQ + t * C::Q_TILE + b * C::Q_BOX, &tmQ, &bar_Q[t], b * C::CPB, q0 + t * 128, bh, kEvictFirst);
+            }
+            for (int j = 0; j < nkv; ++j) {
+                const int s = j % ST;
+                const uint32_t ph = (j / ST) & 1;
+                mbar_wait(&bar_Ke[s], ph ^ 1);
+                mbar_expect_tx(&bar_Kf[s], C::KV_TILE);
+                for (int b = 0; b < C::BOXES; ++b)
+                    tma_load_3d(sK + s * C::KV_TILE + b * C::KV_BOX, &tmK, &bar_Kf[s], b * C::CPB, j * BC, bh, kEvictLast);
+                mbar_wait(&bar_Ve[s], ph ^ 1);
+                mbar_expect_tx(&bar_Vf[s], C::KV_TILE);
+                for (int b = 0; b < C::BOXES; ++b)
+                    tma_load_3d(sV + s * C::KV_TILE + b * C::KV_BOX, &tmV, &bar_Vf[s], b * C::CPB, j * BC, bh, kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ==================================
+        if (lane == 0) {
+            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : kFmtBF16;
+            constexpr uint32_t idesc_S = make_idesc(fmt, 128, BC, false, false);
+            constexpr uint32_t idesc_PV = make_idesc(fmt, 128, D, false, true);
+            const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV);
+
+            auto issue_S = [&](int t, int j) {
+                const int s = j % ST;
+                const uint64_t qd = make_sdesc(q_base + t * C::Q_TILE, 16, 1024, 2);
+                const uint64_t kd = make_sdesc(k_base + s * C::KV_TILE, 16, 1024, 2);
+#pragma unroll
+                for (int kk = 0; kk < D / C::KPER; ++kk) {
+                    const uint32_t inbox = (kk & 3) * 32;
+                    umma_ss<C::kF32>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
+                                     sdesc_advance(kd, (kk >> 2) * C::KV_BOX + inbox), idesc_S, kk > 0);
+                }
+                umma_commit(&bar_S[t]);
+            };
+            auto issue_PV = [&](int t, int j) {
+                const int s = j % ST;
+                const uint64_t vd = make_sdesc(v_base + s * C::KV_TILE, C::KV_BOX, C::V_SBO, C::V_LAYOUT);
+#pragma unroll
+                for (int kk = 0; kk < BC / C::KPER; ++kk)
+                    umma_ts<C::kF32>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
+                                     sdesc_advance(vd, kk * C::KPER * 128), idesc_PV, (j > 0 || kk > 0));
+            };
+
+            mbar_wait(&bar_Kf[0], 0);
+            for (int t = 0; t < ntiles; ++t) {
+                mbar_wait(&bar_Q[t], 0);
+                tc_fence_after();
+                issue_S(t, 0);
+            }
+            umma_commit(&bar_Ke[0]);
+            for (int j = 0; j < nkv; ++j) {
+                const int s = j % ST;
+                mbar_wait(&bar_Vf[s], (j / ST) & 1);
+                if (j + 1 < nkv) mbar_wait(&bar_Kf[(j + 1) % ST], ((j + 1) / ST) & 1);
+                for (int t = 0; t < ntiles; ++t) {
+                    mbar_wait(&bar_P[t], j & 1);
+                    tc_fence_after();
+                    issue_PV(t, j);
+                    if (t == ntiles - 1) umma_commit(&bar_Ve[s]);
+                    if (j + 1 < nkv) {
+                        issue_S(t, j + 1);
+                        if (t == ntiles - 1) umma_commit(&bar_Ke[(j + 1) % ST]);
+                    } else {
+                        umma_commit(&bar_O[t]);
+                    }
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ================================ softmax warpgroups ==========================
+        const int t = (warp - 4) >> 2;
+        if (t < ntiles) softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_P[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv, q0, bh, scale_log2);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------ host side
+template <class C>
+static int launch_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv,
+                      float scale, cudaStream_t st)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(fwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+        attr_set = true;
+    }
+    const CUtensorMapDataType dt = C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapSwizzle v_swz = C::kF32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    const float scale_log2 = scale * 1.4426950408889634f;
+    for (int bh0 = 0; bh0 < BH; bh0 += 65535) {
+        const int nbh = (BH - bh0) < 65535 ? (BH - bh0) : 65535;
+        const size_t qoff = (size_t)bh0 * Nq * C::D * C::EB, koff = (size_t)bh0 * Nkv * C::D * C::EB;
+        CUtensorMap tmQ, tmK, tmV, tmO;
+        if (make_tmap_3d(&tmQ, (const uint8_t*)Q + qoff, dt, C::EB, nbh, Nq, C::D, 128, C::CPB) ||
+            make_tmap_3d(&tmK, (const uint8_t*)K + koff, dt, C::EB, nbh, Nkv, C::D, C::BC, C::CPB) ||
+            make_tmap_3d(&tmV, (const uint8_t*)V + koff, dt, C::EB, nbh, Nkv, C::D, C::BC, C::CPB, v_swz) ||
+            make_tmap_3d(&tmO, (uint8_t*)O + qoff, dt, C::EB, nbh, Nq, C::D, 128, C::CPB))
+            return B200_ERR_CUDA;
+        dim3 grid((Nq + C::NT * 128 - 1) / (C::NT * 128), nbh);
+        fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, L ? L + (size_t)bh0 * Nq : nullptr, Nq, Nkv, scale_log2);
+        B200_CUDA_TRY(cudaGetLastError());
+    }
+    return B200_OK;
+}
+
+bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
+{
+    if (Nq < 1 || Nkv < 1) return false;
+    if (dtype != B200_DTYPE_BF16 && dtype != B200_DTYPE_F32) return false;
+    return d == 64 || d == 128;
+}
+
+int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
+           float scale, int dtype, cudaStream_t st)
+{
+    const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
+    if ((align & 15) != 0 || !(scale > 0.0f))      // TMA needs 16-byte bases; max(S)*scale needs scale > 0
+        return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
+    if (dtype == B200_DTYPE_BF16) {
+        if (d == 128) return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+    }
+    if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+    return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+}
+
+}  // namespace b200

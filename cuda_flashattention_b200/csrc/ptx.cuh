@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 #include <cuda.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace b200 {
 
@@ -190,11 +191,16 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t fmt_ab, int M, int N,
 // MN-major operand (rows of 128 B = 64/32 elements along MN; 8 K-rows per 1024 B group):
 //   SBO = byte distance between consecutive 8-row K groups, LBO = byte distance between
 //   consecutive 128-byte MN chunks.
-__host__ __device__ constexpr uint64_t make_sdesc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte atoms); 1 = SWIZZLE_128B_BASE32B (32-byte atoms, 4-row pattern: the only
+// layout the hardware accepts for MN-major tf32 operands; TMA counterpart CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B).
+__host__ __device__ constexpr uint64_t make_sdesc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
     return static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4) |
            (static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16) |
            (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32) |
-           (1ull << 46) | (2ull << 61);
+           (1ull << 46) | (static_cast<uint64_t>(layout) << 61);
+}
+__host__ __device__ constexpr uint64_t make_sdesc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return make_sdesc(smem_addr, lbo_bytes, sbo_bytes, 2);
 }
 // Advancing the start address of an existing descriptor by `bytes` (bytes % 16 == 0, no carry out of 14 bits)
 __host__ __device__ constexpr uint64_t sdesc_advance(uint64_t desc, uint32_t bytes) { return desc + (bytes >> 4); }

@@ -71,6 +71,11 @@ B200_API int b200_version(void);
 B200_API int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
 B200_API int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
 
+/* Test hook: non-zero routes every call to the generic CUDA-core kernels (used by the GPU tests to
+ * cross-check the tensor-core kernels on the device at sizes the CPU oracle cannot reach).
+ * Returns the previous setting.  Not a fallback: both families are GPU code in this library. */
+B200_API int b200_debug_force_generic(int on);
+
 /* ---- reference-signature entry points (one head, fp32) -------------------------------------- */
 
 /* Replaces flash_attention_2_forward(Q,K,V,O,L,seq_len,head_dim,softmax_scale):

@@ -20,7 +20,7 @@ struct ProbeParams {
     int a_boxes, a_box_rows, b_boxes, b_box_rows;
     uint32_t a_lbo, a_sbo, a_kadv, a_steps_per_box, a_box_stride;
     uint32_t b_lbo, b_sbo, b_kadv, b_steps_per_box, b_box_stride;
-    uint32_t idesc;
+    uint32_t idesc, a_layout, b_layout;
     int ksteps, N, Ktot;
     int a_tmem_cols_per_step;
     const void* A_gmem;    // row-major [128][Ktot] (modes 1, 2)
@@ -102,8 +102,8 @@ probe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (tid == 0) {
         mbar_wait(&bar_load, 0);
         tc_fence_after();
-        const uint64_t adesc0 = make_sdesc_sw128(smem_u32(sA), p.a_lbo, p.a_sbo);
-        const uint64_t bdesc0 = make_sdesc_sw128(smem_u32(sB), p.b_lbo, p.b_sbo);
+        const uint64_t adesc0 = make_sdesc(smem_u32(sA), p.a_lbo, p.a_sbo, p.a_layout);
+        const uint64_t bdesc0 = make_sdesc(smem_u32(sB), p.b_lbo, p.b_sbo, p.b_layout);
         for (int s = 0; s < p.ksteps; ++s) {
             uint32_t aoff = (s / p.a_steps_per_box) * p.a_box_stride + (s % p.a_steps_per_box) * p.a_kadv;
             uint32_t boff = (s / p.b_steps_per_box) * p.b_box_stride + (s % p.b_steps_per_box) * p.b_kadv;
@@ -146,6 +146,7 @@ struct Case {
     bool a_mn, b_mn;          // operand storage: false = [rows=MN][cols=K] (K-major), true = [rows=K][cols=MN] (MN-major)
     int N, K;
     bool swap_a, swap_b;      // alternative hypothesis: swap LBO/SBO roles
+    int atom32;               // MN-major operands use the 32-byte-atom 128B swizzle; value = SBO in bytes (0 = off)
 };
 
 int main(int argc, char** argv)
@@ -167,6 +168,12 @@ int main(int argc, char** argv)
         {"bf16 NT  SS  N=256                     K=64 ", 2, 0, false, false, 256, 64, false, false},
         {"bf16 NT  SS  N=64 K=64 (d=64 S tile)        ", 2, 0, false, false, 64, 64, false, false},
         {"tf32 NN  SS  N=64 (V MN-major)         K=64 ", 4, 0, false, true, 64, 64, false, false},
+        {"tf32 NN  SS  V MN-major ATOM_32B SBO=512    ", 4, 0, false, true, 128, 64, false, false, 512},
+        {"tf32 NN  SS  V MN-major ATOM_32B SBO=1024   ", 4, 0, false, true, 128, 64, false, false, 1024},
+        {"tf32 NN  TS  P in TMEM, V ATOM_32B SBO=512  ", 4, 1, false, true, 128, 64, false, false, 512},
+        {"tf32 TN  SS  A MN-major ATOM_32B SBO=512    ", 4, 0, true, false, 128, 64, false, false, 512},
+        {"tf32 NN  SS  N=64 V ATOM_32B SBO=512   K=128", 4, 0, false, true, 64, 128, false, false, 512},
+        {"tf32 NT  TS  P in TMEM, B K-major           ", 4, 1, false, false, 128, 64, false, false, 0},
     };
     const int ncases = sizeof(cases) / sizeof(cases[0]);
     if (argc < 2) { printf("%d\n", ncases); return 0; }
@@ -204,7 +211,9 @@ int main(int argc, char** argv)
 
     CUtensorMap tmA, tmB;
     CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
-    if (make_tmap_3d(&tmA, dA, dt, eb, 1, ar, ac, ar, cpb) || make_tmap_3d(&tmB, dB, dt, eb, 1, br, bc, br, cpb)) {
+    CUtensorMapSwizzle swA = (c.atom32 && c.a_mn) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    CUtensorMapSwizzle swB = (c.atom32 && c.b_mn) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    if (make_tmap_3d(&tmA, dA, dt, eb, 1, ar, ac, ar, cpb, swA) || make_tmap_3d(&tmB, dB, dt, eb, 1, br, bc, br, cpb, swB)) {
         printf("tensor map encode failed\n"); return 2;
     }
 
@@ -223,6 +232,9 @@ int main(int argc, char** argv)
     };
     fill(c.a_mn, ar, ac, c.swap_a, p.a_boxes, p.a_box_rows, p.a_lbo, p.a_sbo, p.a_kadv, p.a_steps_per_box, p.a_box_stride);
     fill(c.b_mn, br, bc, c.swap_b, p.b_boxes, p.b_box_rows, p.b_lbo, p.b_sbo, p.b_kadv, p.b_steps_per_box, p.b_box_stride);
+    p.a_layout = 2; p.b_layout = 2;
+    if (c.atom32 && c.a_mn) { p.a_layout = 1; p.a_sbo = c.atom32; }
+    if (c.atom32 && c.b_mn) { p.b_layout = 1; p.b_sbo = c.atom32; }
     p.a_tmem_cols_per_step = 8;    // bf16: 16 K-elements packed 2/column; tf32: 8 K-elements 1/column
     p.idesc = make_idesc(eb == 2 ? kFmtBF16 : kFmtTF32, M, N, c.a_mn, c.b_mn);
 
