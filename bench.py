@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the exact-attention hot path (contract: see the task brief).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json north_star / configs):
+  N = 1 : C3  FA2 forward+backward, B=8 H=16 N=8192 d=128 bf16, one step = fwd then bwd of the whole batch.
+  N > 1 : ring attention forward+backward with the SAME per-GPU FLOPs (weak scaling): every rank
+          holds N_local = 8192 rows of B*H = 128/N heads, total sequence 8192*N (N = 8 is exactly
+          C4's shape: B=1 H=16 N=65536 d=128).
+Metric: attention TFLOP/s, algorithmic FLOPs 14*B*H*Nq*Nkv*d (4 fwd + 10 bwd), whole job.
+`value` is measured with inputs resident in HBM; `e2e` goes through the same C-ABI calls with HOST
+(pinned) buffers, host<->device copies of every input and output inside the timed region.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "attention TFLOP/s (FA2 fwd+bwd, algorithmic 14*B*H*N^2*d), whole job"
+UNIT = "TFLOP/s"
+B0, H0, N0, D0 = 8, 16, 8192, 128
+
+
+def workload(n_gpus):
+    """(B, H, N_local, N_total, d) per the weak-scaling series described above."""
+    bh = (B0 * H0) // n_gpus
+    H = H0
+    B = max(1, bh // H)
+    if B * H != bh:
+        H = bh; B = 1
+    return B, H, N0, N0 * n_gpus, D0
+
+
+def config_dict(n_gpus):
+    B, H, Nl, Nt, d = workload(n_gpus)
+    name = ("C3 FA2 fwd+bwd B=8 H=16 N=8192 d=128 bf16" if n_gpus == 1 else
+            f"ring fwd+bwd B={B} H={H} N={Nt} d={d} bf16 over {n_gpus} GPUs (N_local={Nl}; C4 shape at 8 GPUs)")
+    return {"workload": name, "B": B, "H": H, "N_total": Nt, "N_local": Nl, "d": d,
+            "parallelism": "single" if n_gpus == 1 else f"ring-sp{n_gpus}",
+            "l2_policy": "inputs larger than L2 (4 x 268 MB bf16 tensors vs 126 MB L2)"}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            j = json.load(f)
+        return {"src": "measured", "burst": float(j["bf16_tflops"]), "sustained": float(j.get("bf16_tflops_sustained", j["bf16_tflops"])),
+                "hbm": float(j["hbm_gbs"])}
+    return {"src": "fallback", "burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons during the timed region (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        self.stop_flag = True
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        s = sorted(self.sm)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the reference's own CPU attention (oracle/_ref when it was compiled in the build
+# container, else our C port), one (head) call per host thread -- the functions themselves are
+# single-threaded (reference README.md:65).
+# --------------------------------------------------------------------------------------------
+def cpu_sample(n_heads, N, d):
+    """fwd+bwd of n_heads independent heads of length N on n_heads host threads; returns seconds."""
+    import numpy as np
+    import oracle
+    rng = np.random.default_rng(0)
+    data = [[rng.standard_normal((N, d)).astype(np.float32) for _ in range(4)] for _ in range(n_heads)]
+    use_ref = oracle.ref_available()
+    sc = float(1.0 / np.sqrt(np.float32(d)))
+
+    def one(i):
+        Q, K, V, dO = data[i]
+        if use_ref:
+            oracle.ref_forward_pass(Q, K, V, sc)
+            oracle.ref_backward(Q, K, V, dO, sc)
+        else:
+            oracle.forward(Q, K, V, sc)
+            oracle.backward_jacobian(Q, K, V, dO, sc)
+
+    oracle.lib()
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=one, args=(i,)) for i in range(n_heads)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    return time.perf_counter() - t0, ("reference" if use_ref else "port")
+
+
+def cpu_baseline(N=768, d=D0):
+    cores = os.cpu_count() or 1
+    heads = min(cores, 32)
+    secs, kind = cpu_sample(heads, N, d)
+    flops = 14.0 * heads * N * N * d
+    return {"value": flops / secs / 1e12, "unit": UNIT, "cores": heads, "kind": kind,
+            "sample": f"{heads} heads x (naive_forward_pass + naive_attention_backward) at N={N} d={d} fp32, one head per host thread, {secs:.2f} s"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    N = 512                                    # the naive backward is O(N^3): keep each step a few seconds
+    for _ in range(args.warmup):
+        cpu_sample(min(os.cpu_count() or 1, 32), 256, D0)
+    times, kind, heads = [], "port", min(os.cpu_count() or 1, 32)
+    for _ in range(args.steps):
+        s, kind = cpu_sample(heads, N, D0)
+        times.append(s)
+    per = sum(times) / len(times)
+    val = 14.0 * heads * N * N * D0 / per / 1e12
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config_dict(args.gpus),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": heads, "kind": kind,
+                             "sample": f"each step: {heads} heads x fwd+bwd at N={N} d={D0} fp32 on {heads} host threads"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import cuda_flashattention_b200 as fa
+    from cuda_flashattention_b200._lib import lib, check
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local_rank)
+    comm = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        comm = fa.RingComm()
+    B, H, Nl, Nt, d = workload(world)
+    g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+    mk = lambda: torch.randn(B, H, Nl, d, device="cuda", dtype=torch.float32, generator=g).to(torch.bfloat16)
+    q, k, v, dO = mk(), mk(), mk(), mk() * 0.2
+    O, dQ, dK, dV = [torch.empty_like(q) for _ in range(4)]
+    L = torch.empty(B, H, Nl, device="cuda", dtype=torch.float32)
+    st = torch.cuda.current_stream().cuda_stream
+    P = lambda t: t.data_ptr()
+    ch = comm.handle if comm else None
+
+    def fwd():
+        if world == 1:
+            check(lib.b200_fa2_fwd(P(q), P(k), P(v), P(O), P(L), B, H, Nl, Nl, d, 0.0, 0, st), "fwd")
+        else:
+            check(lib.b200_ring_fwd(P(q), P(k), P(v), P(O), P(L), B, H, Nl, d, 0.0, 0, ch, rank, world, st), "ring_fwd")
+
+    def bwd():
+        if world == 1:
+            check(lib.b200_fa2_bwd(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, Nl, d, 0.0, 0, None, 0, st), "bwd")
+        else:
+            check(lib.b200_ring_bwd(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, d, 0.0, 0, ch, rank, world, st), "ring_bwd")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        fwd(); bwd()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+    launches0 = lib.b200_debug_launch_count()
+    ev[0].record()
+    for i in range(args.steps):
+        fwd(); ev[2 * i + 1].record()
+        bwd(); ev[2 * i + 2].record()
+    barrier()
+    launches = (lib.b200_debug_launch_count() - launches0) // args.steps
+    clocks = sampler.result()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    fwd_ms = sum(ev[2 * i].elapsed_time(ev[2 * i + 1]) for i in range(args.steps)) / args.steps
+    bwd_ms = sum(ev[2 * i + 1].elapsed_time(ev[2 * i + 2]) for i in range(args.steps)) / args.steps
+    t = torch.tensor([total_ms, fwd_ms, bwd_ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, fwd_ms, bwd_ms = [float(x) for x in t.tolist()]
+    ms_per_step = total_ms / args.steps
+    flops_rank = 14.0 * B * H * Nl * Nt * d
+    value = world * flops_rank / (ms_per_step * 1e-3) / 1e12
+
+    # ---- end to end: host (pinned) buffers in, host buffers out, copies inside the timed region
+    hin = [torch.empty_like(x, device="cpu").pin_memory().copy_(x) for x in (q, k, v, dO)]
+    hout = [torch.empty_like(x, device="cpu").pin_memory() for x in (O, dQ, dK, dV)]
+    hL = torch.empty_like(L, device="cpu").pin_memory()
+
+    def e2e_step():
+        for dst, src in zip((q, k, v, dO), hin):
+            dst.copy_(src, non_blocking=True)
+        fwd(); bwd()
+        for dst, src in zip(hout, (O, dQ, dK, dV)):
+            dst.copy_(src, non_blocking=True)
+        hL.copy_(L, non_blocking=True)
+
+    e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_e2e = max(1, min(args.steps, 5))
+    e0.record()
+    for _ in range(n_e2e):
+        e2e_step()
+    e1.record()
+    barrier()
+    t2 = torch.tensor([e0.elapsed_time(e1) / n_e2e], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t2.item())
+    h2d = sum(x.numel() * x.element_size() for x in hin)
+    d2h = sum(x.numel() * x.element_size() for x in hout) + hL.numel() * 4
+
+    if rank == 0:
+        pk = peaks()
+        tc_bwd = bool(lib.b200_bwd_uses_tensor_cores(0, d, Nl, Nl))
+        dom = "bwd" if bwd_ms >= fwd_ms else "fwd"
+        dom_flops = (10.0 if dom == "bwd" else 4.0) * B * H * Nl * Nt * d
+        dom_ms = bwd_ms if dom == "bwd" else fwd_ms
+        achieved = dom_flops / (dom_ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic", "config": config_dict(world),
+            "fwd": {"ms": fwd_ms, "tflops_per_gpu": 4.0 * B * H * Nl * Nt * d / (fwd_ms * 1e-3) / 1e12},
+            "bwd": {"ms": bwd_ms, "tflops_per_gpu": 10.0 * B * H * Nl * Nt * d / (bwd_ms * 1e-3) / 1e12,
+                    "kernel_family": "tcgen05" if tc_bwd else "generic CUDA-core (tcgen05 backward not built yet)"},
+            "pct_of_nominal_2250": 100.0 * value / world / 2250.0,
+            "roofline": {"bound": "tensor", "kernel": f"{dom} ({'whole ring pass incl. merge/accumulate kernels' if world > 1 else 'call incl. its small helper kernels'})",
+                         "achieved": achieved, "peak": pk["sustained"], "peak_src": f"{pk['src']} sustained bf16 (timed inside the step loop)",
+                         "unit": "TFLOP/s", "frac": achieved / pk["sustained"], "traffic": None},
+            "e2e": {"value": world * flops_rank / (e2e_ms * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line))
+    if world > 1:
+        comm.close()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

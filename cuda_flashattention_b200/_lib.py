@@ -27,6 +27,7 @@ _SIGS = {
     "b200_last_cuda_error": (_i, []),
     "b200_version": (_i, []),
     "b200_debug_force_generic": (_i, [_i]),
+    "b200_debug_launch_count": (C.c_ulonglong, []),
     "b200_fwd_uses_tensor_cores": (_i, [_i, _i, _i, _i]),
     "b200_bwd_uses_tensor_cores": (_i, [_i, _i, _i, _i]),
     "b200_fa2_fwd_f32": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _f, _vp]),

@@ -8,6 +8,8 @@ namespace b200 {
 
 static thread_local int g_last_cuda_error = 0;
 void set_last_cuda_error(int code) { g_last_cuda_error = code; }
+static unsigned long long g_launches = 0;
+void count_launch(int n) { g_launches += (unsigned long long)n; }
 
 struct Arena { void* ptr = nullptr; size_t bytes = 0; };
 static Arena g_arena[64];
@@ -125,6 +127,7 @@ const char* b200_strerror(int s)
 }
 int b200_last_cuda_error(void) { return g_last_cuda_error; }
 int b200_version(void) { return 100; }
+unsigned long long b200_debug_launch_count(void) { return g_launches; }
 int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generic = on ? 1 : 0; return old; }
 
 int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }

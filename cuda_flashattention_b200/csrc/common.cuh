@@ -9,6 +9,7 @@
 namespace b200 {
 
 void set_last_cuda_error(int code);
+void count_launch(int n = 1);       // bookkeeping for b200_debug_launch_count()
 
 #define B200_CUDA_TRY(call)                                   \
     do {                                                      \

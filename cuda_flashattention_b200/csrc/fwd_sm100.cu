@@ -339,6 +339,7 @@ static int launch_fwd(const void* Q, const void* K, const void* V, void* O, floa
         dim3 grid((Nq + C::NT * 128 - 1) / (C::NT * 128), nbh);
         fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, L ? L + (size_t)bh0 * Nq : nullptr, Nq, Nkv, scale_log2);
         B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     }
     return B200_OK;
 }

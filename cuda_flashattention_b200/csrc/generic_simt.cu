@@ -309,6 +309,7 @@ static int simt_fwd_t(const T* Q, const T* K, const T* V, T* O, float* L, float*
     dim3 grid((Nq + kSimtWarps - 1) / kSimtWarps, BH);
     simt_fwd_kernel<T><<<grid, kSimtWarps * 32, smem, st>>>(Q, K, V, O, L, M, Nq, Nkv, d, scale, mode);
     B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     return B200_OK;
 }
 
@@ -329,6 +330,7 @@ static int rowdot_t(const T* dO, const T* O, float* D, size_t rows, int d, cudaS
     if (rows == 0) return B200_OK;
     rowdot_kernel<T><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(dO, O, D, rows, d);
     B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     return B200_OK;
 }
 int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtype, cudaStream_t st)
@@ -348,11 +350,13 @@ static int simt_bwd_t(const T* Q, const T* K, const T* V, const T* dO, const flo
         dim3 g1((Nq + kSimtWarps - 1) / kSimtWarps, BH);
         simt_bwd_dq_kernel<T><<<g1, kSimtWarps * 32, s1, st>>>(Q, K, V, dO, L, D, dQ, Nq, Nkv, d, scale);
         B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     }
     if (dK && dV) {
         dim3 g2((Nkv + kSimtWarps - 1) / kSimtWarps, BH);
         simt_bwd_dkv_kernel<T><<<g2, kSimtWarps * 32, s2, st>>>(Q, K, V, dO, L, D, dK, dV, Nq, Nkv, d, scale);
         B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     }
     return B200_OK;
 }
@@ -376,6 +380,7 @@ int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows,
     if (dtype == B200_DTYPE_F32) lse_merge_kernel<float><<<grid, 256, 0, st>>>((float*)Oa, La, (const float*)Ob, Lb, rows, d);
     else lse_merge_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)Oa, La, (const __nv_bfloat16*)Ob, Lb, rows, d);
     B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     return B200_OK;
 }
 

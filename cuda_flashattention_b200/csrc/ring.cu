@@ -104,6 +104,7 @@ static int accum(float* acc, const void* part, size_t n, int dtype, cudaStream_t
     if (dtype == B200_DTYPE_F32) accum_kernel<float><<<grid, 256, 0, st>>>(acc, (const float*)part, n);
     else accum_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(acc, (const __nv_bfloat16*)part, n);
     B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     return B200_OK;
 }
 static int cast_out(void* out, const float* acc, size_t n, int dtype, cudaStream_t st)
@@ -113,6 +114,7 @@ static int cast_out(void* out, const float* acc, size_t n, int dtype, cudaStream
     if (dtype == B200_DTYPE_F32) cast_kernel<float><<<grid, 256, 0, st>>>((float*)out, acc, n);
     else cast_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)out, acc, n);
     B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
     return B200_OK;
 }
 

@@ -75,6 +75,8 @@ B200_API int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
  * cross-check the tensor-core kernels on the device at sizes the CPU oracle cannot reach).
  * Returns the previous setting.  Not a fallback: both families are GPU code in this library. */
 B200_API int b200_debug_force_generic(int on);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches claim). */
+B200_API unsigned long long b200_debug_launch_count(void);
 
 /* ---- reference-signature entry points (one head, fp32) -------------------------------------- */
 
