@@ -1,8 +1,400 @@
-// placeholder until the tcgen05 backward lands
+// bwd_sm100.cu -- FlashAttention-2 backward for sm_100a (bf16, d = 128): dK/dV-stationary CTAs,
+// tcgen05 MMAs with every accumulator in TMEM, dQ reduced into an fp32 buffer by TMA reduce-add.
+//
+// Replaces flash_attention_2_backward_kernel (reference
+// src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:47-246).  Same math --
+// P = exp(S - L), dP = dO V^T, dS = P o (dP - D), dV += P^T dO, dK += scale dS^T Q,
+// dQ += scale dS K with D = rowsum(dO o O) -- but the loop order is the one north_star asks for:
+// a CTA owns one 128-row K/V tile (dK, dV accumulate in TMEM for the whole kernel, no atomics on
+// them) and streams 64-row Q/dO tiles; the reference is dQ-stationary with smem + global atomics
+// on dK/dV and 32x redundant dQ math (:196-231).
+//
+// Everything is computed TRANSPOSED so that a thread owns a kv row (TMEM lane):
+//   M1  S^T  = K Q_i^T              SS   [128 kv x 64 q]   -> TMEM S[b] (double buffered)
+//   M2  dP^T = V dO_i^T             SS   [128 kv x 64 q]   -> TMEM dP
+//   compute warpgroups: P^T = exp2(S^T c - L_i log2e) -> TMEM (bf16, aliasing S[b]);
+//                       dS^T = scale P^T o (dP^T - D_i) -> TMEM (bf16, aliasing dP) and smem
+//   M3  dV  += P^T dO_i             TS   A = P^T from TMEM, B = dO_i as an MN-major operand
+//   M4  dK  += dS^T Q_i             TS   A = dS^T from TMEM, B = Q_i as an MN-major operand
+//   M5  dQ_i^T = K^T dS             SS   A = K (MN-major view), B = dS^T smem (MN-major) -> TMEM dQ
+//   drain warpgroup: dQ_i^T TMEM -> registers -> smem [64 q][128 d] fp32 -> cp.reduce.async.bulk (add)
+// TMEM columns: S[0] 0..63, S[1] 64..127, dP 128..191, dQ^T 192..255, dV 256..383, dK 384..511.
+// Issue order per iteration i:  M1(i+1) | M3(i) M4(i) | M2(i+1) | M5(i)   (see DESIGN.md for the slack analysis)
+//
+// Warps: 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 4-7 and 8-11 compute warpgroups (q columns
+// 0-31 / 32-63 of the same kv rows), 12-15 dQ drain.
 #include "common.cuh"
+#include "ptx.cuh"
+#include "tmap.h"
+
 namespace b200 {
-bool tc_bwd_supported(int, int, int, int) { return false; }
-size_t tc_bwd_workspace_bytes(int, int, int, int, int) { return 0; }
-int tc_bwd(const void*, const void*, const void*, const void*, const float*, const float*, void*, void*, void*, int, int, int, int,
-           float, int, void*, size_t, cudaStream_t) { return B200_ERR_UNSUPPORTED; }
+
+namespace bwd {
+constexpr int D = 128, BN = 128, BM = 64, NS = 3;
+constexpr int KV_BOX = BN * 128, KV_TILE = 2 * KV_BOX;        // 32 KB: [128 rows x 128 d] bf16 as 2 boxes of 64 d
+constexpr int Q_BOX = BM * 128, Q_TILE = 2 * Q_BOX;           // 16 KB: [64 rows x 128 d]
+constexpr int DS_TILE = BN * 128;                             // 16 KB: dS^T [128 kv rows x 64 q] bf16
+constexpr int DQ_STAGE = BM * D * 4;                          // 32 KB: [64 q][128 d] fp32
+constexpr int STAT_BYTES = BM * 4;                            // 256 B of L (or D) per Q tile
+constexpr int THREADS = 512;
+// smem carve-up (offsets from the 1024-aligned base)
+constexpr int OFF_K = 0, OFF_V = OFF_K + KV_TILE, OFF_Q = OFF_V + KV_TILE, OFF_DO = OFF_Q + NS * Q_TILE;
+constexpr int OFF_DS = OFF_DO + NS * Q_TILE, OFF_DQ = OFF_DS + 2 * DS_TILE, OFF_STAT = OFF_DQ + DQ_STAGE;
+constexpr int OFF_BAR = OFF_STAT + NS * 2 * STAT_BYTES;
+constexpr int NBARS = 1 + 2 * NS + 2 + 1 + 2 + 1 + 2 + 1;
+constexpr int SMEM = 1024 + OFF_BAR + NBARS * 8 + 16;
+static_assert(SMEM <= 227 * 1024, "backward shared memory budget");
+constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DQ = 192, TM_DV = 256, TM_DK = 384;
+}  // namespace bwd
+
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+
+// One compute warpgroup (w = 0/1 owns q columns 32w..32w+31 of every Q tile; thread = kv row).
+__device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* smem, uint64_t* bar_in_full,
+                                                 uint64_t* bar_S, uint64_t* bar_dP, uint64_t* bar_P, uint64_t* bar_dS,
+                                                 int n_q, float scale_log2, float scale)
+{
+    using namespace bwd;
+    const int r = threadIdx.x & 127;                                   // kv row within the tile == TMEM lane
+    const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
+    for (int i = 0; i < n_q; ++i) {
+        const int b = i & 1, s = i % NS;
+        const float* Lq = reinterpret_cast<const float*>(smem + OFF_STAT + s * 2 * STAT_BYTES) + 32 * w;
+        const float* Dq = Lq + BM;
+        const uint32_t tS = tmem + TM_S + 64 * b + 32 * w + lane_base;
+        const uint32_t tP = tmem + TM_DP + 32 * w + lane_base;
+        // ---- P^T = exp2(S^T * scale*log2e - L*log2e)
+        mbar_wait(&bar_in_full[s], (i / NS) & 1);                       // L_i, D_i landed (same barrier as Q_i, dO_i)
+        mbar_wait(&bar_S[b], (i >> 1) & 1);
+        tc_fence_after();
+        uint32_t sv[32];
+        B200_TMEM_LD_32(tS, sv);
+        tmem_wait_ld();
+        float p[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -Lq[c]));
+        {
+            uint32_t pk[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) pk[c] = pack_bf16x2(p[2 * c], p[2 * c + 1]);
+            B200_TMEM_ST_16(tS, pk);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(&bar_P[b]);
+        // ---- dS^T = scale * P^T o (dP^T - D)
+        mbar_wait(bar_dP, i & 1);
+        tc_fence_after();
+        B200_TMEM_LD_32(tP, sv);
+        tmem_wait_ld();
+        uint32_t dk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            const float a0 = p[2 * c] * (__uint_as_float(sv[2 * c]) - Dq[2 * c]) * scale;
+            const float a1 = p[2 * c + 1] * (__uint_as_float(sv[2 * c + 1]) - Dq[2 * c + 1]) * scale;
+            dk[c] = pack_bf16x2(a0, a1);
+        }
+        B200_TMEM_ST_16(tP, dk);
+        // smem copy (B operand of M5): row r = 128 B, this warpgroup owns 16-byte chunks 4w..4w+3
+        uint8_t* rowp = smem + OFF_DS + b * DS_TILE + r * 128;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<uint4*>(rowp + (((4 * w + q) ^ (r & 7)) * 16)) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+        fence_proxy_async_smem();
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_dS);
+    }
+}
+
+// dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> smem [64 q][128 d] fp32 -> TMA reduce-add.
+__device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint8_t* smem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
+                                               const CUtensorMap* tmdQ, int n_q, int bh)
+{
+    using namespace bwd;
+    const int r = threadIdx.x & 127;                                   // d index == TMEM lane
+    const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
+    float* stage = reinterpret_cast<float*>(smem + OFF_DQ);
+    for (int i = 0; i < n_q; ++i) {
+        mbar_wait(bar_dQ_full, i & 1);
+        tc_fence_after();
+        uint32_t v[64];
+        B200_TMEM_LD_32(tQ, v);
+        B200_TMEM_LD_32(tQ + 32, v + 32);
+        tmem_wait_ld();
+        tc_fence_before();
+        mbar_arrive(bar_dQ_empty);                                     // TMEM columns are free again
+        if (r == 0) tma_store_wait_read<0>();                          // previous reduce has finished reading the stage
+        named_bar_sync(3, 128);
+#pragma unroll
+        for (int q = 0; q < 64; ++q) stage[q * D + r] = __uint_as_float(v[q]);   // a warp writes 32 consecutive floats
+        fence_proxy_async_smem();
+        named_bar_sync(3, 128);
+        if (r == 0) { tma_reduce_add_3d(tmdQ, stage, 0, i * BM, bh); tma_store_commit(); }
+    }
+    if (r == 0) tma_store_wait<0>();
+}
+
+// dV (w = 0) / dK (w = 1) epilogue: TMEM fp32 [128 kv x 128 d] -> bf16 -> swizzled smem -> TMA store.
+__device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem, const CUtensorMap* tm, int kv0, int bh)
+{
+    using namespace bwd;
+    const int r = threadIdx.x & 127;
+    const uint32_t tA = tmem + (w == 0 ? TM_DV : TM_DK) + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
+    uint8_t* out = smem + (w == 0 ? OFF_V : OFF_K);                    // K / V tiles are dead after the last MMA
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        B200_TMEM_LD_32(tA + 32 * c, o);
+        tmem_wait_ld();
+        uint8_t* rowp = out + (c >> 1) * KV_BOX + r * 128;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(o[8 * q]), __uint_as_float(o[8 * q + 1]));
+            v.y = pack_bf16x2(__uint_as_float(o[8 * q + 2]), __uint_as_float(o[8 * q + 3]));
+            v.z = pack_bf16x2(__uint_as_float(o[8 * q + 4]), __uint_as_float(o[8 * q + 5]));
+            v.w = pack_bf16x2(__uint_as_float(o[8 * q + 6]), __uint_as_float(o[8 * q + 7]));
+            *reinterpret_cast<uint4*>(rowp + ((((c & 1) * 4 + q) ^ (r & 7)) * 16)) = v;
+        }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(4 + w, 128);
+    if (r == 0) {
+        tma_store_3d(tm, out, 0, kv0, bh);
+        tma_store_3d(tm, out + KV_BOX, 64, kv0, bh);
+        tma_store_commit();
+        tma_store_wait<0>();
+    }
+}
+
+__global__ void __launch_bounds__(bwd::THREADS, 1)
+bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+           const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+           const __grid_constant__ CUtensorMap tmdQ, const __grid_constant__ CUtensorMap tmdK,
+           const __grid_constant__ CUtensorMap tmdV, const float* __restrict__ L2p, const float* __restrict__ Dp,
+           int Nq, int Nq_pad, float scale_log2, float scale)
+{
+    using namespace bwd;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+    uint64_t* bar_KV = bars;                     // [1]
+    uint64_t* bar_in_full = bar_KV + 1;          // [NS]  Q_i, dO_i, L_i, D_i landed
+    uint64_t* bar_in_empty = bar_in_full + NS;   // [NS]
+    uint64_t* bar_S = bar_in_empty + NS;         // [2]   S^T(i) complete
+    uint64_t* bar_dP = bar_S + 2;                // [1]   dP^T(i) complete
+    uint64_t* bar_P = bar_dP + 1;                // [2]   P^T(i) written (256 arrivals)
+    uint64_t* bar_dS = bar_P + 2;                // [1]   dS^T(i) written to TMEM + smem (256 arrivals)
+    uint64_t* bar_dQ_full = bar_dS + 1;          // [1]
+    uint64_t* bar_dQ_empty = bar_dQ_full + 1;    // [1]   (128 arrivals)
+    uint64_t* bar_done = bar_dQ_empty + 1;       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bh = blockIdx.y, kv0 = blockIdx.x * BN;
+    const int n_q = (Nq + BM - 1) / BM;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_KV, 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&bar_in_full[s], 1); mbar_init(&bar_in_empty[s], 1); }
+        mbar_init(&bar_S[0], 1); mbar_init(&bar_S[1], 1); mbar_init(bar_dP, 1);
+        mbar_init(&bar_P[0], 256); mbar_init(&bar_P[1], 256); mbar_init(bar_dS, 256);
+        mbar_init(bar_dQ_full, 1); mbar_init(bar_dQ_empty, 128); mbar_init(bar_done, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmdO);
+        tma_prefetch_desc(&tmdQ); tma_prefetch_desc(&tmdK); tma_prefetch_desc(&tmdV);
+    }
+    if (warp == 2) { tmem_alloc<512>(tmem_slot); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            mbar_expect_tx(bar_KV, 2 * KV_TILE);
+            for (int b = 0; b < 2; ++b) {
+                tma_load_3d(smem + OFF_K + b * KV_BOX, &tmK, bar_KV, b * 64, kv0, bh, kEvictFirst);
+                tma_load_3d(smem + OFF_V + b * KV_BOX, &tmV, bar_KV, b * 64, kv0, bh, kEvictFirst);
+            }
+            const float* Lrow = L2p + (size_t)bh * Nq_pad;
+            const float* Drow = Dp + (size_t)bh * Nq_pad;
+            for (int i = 0; i < n_q; ++i) {
+                const int s = i % NS;
+                mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
+                mbar_expect_tx(&bar_in_full[s], 2 * Q_TILE + 2 * STAT_BYTES);
+                for (int b = 0; b < 2; ++b) {
+                    tma_load_3d(smem + OFF_Q + s * Q_TILE + b * Q_BOX, &tmQ, &bar_in_full[s], b * 64, i * BM, bh, kEvictLast);
+                    tma_load_3d(smem + OFF_DO + s * Q_TILE + b * Q_BOX, &tmdO, &bar_in_full[s], b * 64, i * BM, bh, kEvictLast);
+                }
+                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES, Lrow + i * BM, STAT_BYTES, &bar_in_full[s]);
+                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES + STAT_BYTES, Drow + i * BM, STAT_BYTES, &bar_in_full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ==================================
+        if (lane == 0) {
+            constexpr uint32_t idesc_ss = make_idesc(kFmtBF16, 128, BM, false, false);   // M1, M2
+            constexpr uint32_t idesc_ts = make_idesc(kFmtBF16, 128, D, false, true);     // M3, M4
+            constexpr uint32_t idesc_dq = make_idesc(kFmtBF16, 128, BM, true, true);     // M5
+            const uint32_t sb = smem_u32(smem);
+            auto mma_ss = [&](uint32_t a_tile, uint32_t b_tile, uint32_t d_col) {        // D = A[128 x d] B[64 x d]^T
+                const uint64_t ad = make_sdesc(a_tile, 16, 1024, 2), bd = make_sdesc(b_tile, 16, 1024, 2);
+#pragma unroll
+                for (int kk = 0; kk < D / 16; ++kk)
+                    umma_f16_ss(tmem + d_col, sdesc_advance(ad, (kk >> 2) * KV_BOX + (kk & 3) * 32),
+                                sdesc_advance(bd, (kk >> 2) * Q_BOX + (kk & 3) * 32), idesc_ss, kk > 0);
+            };
+            auto mma_ts = [&](uint32_t a_col, uint32_t b_tile, uint32_t d_col, bool acc) {   // D += A^T-in-TMEM[128 x 64] B[64 x d]
+                const uint64_t bd = make_sdesc(b_tile, Q_BOX, 1024, 2);
+#pragma unroll
+                for (int kk = 0; kk < BM / 16; ++kk)
+                    umma_f16_ts(tmem + d_col, tmem + a_col + (kk < 2 ? 8 * kk : 32 + 8 * (kk - 2)),
+                                sdesc_advance(bd, kk * 2048), idesc_ts, (acc || kk > 0) ? 1u : 0u);
+            };
+            auto M1 = [&](int i) { mma_ss(sb + OFF_K, sb + OFF_Q + (i % NS) * Q_TILE, TM_S + 64 * (i & 1)); umma_commit(&bar_S[i & 1]); };
+            auto M2 = [&](int i) { mma_ss(sb + OFF_V, sb + OFF_DO + (i % NS) * Q_TILE, TM_DP); umma_commit(bar_dP); };
+
+            mbar_wait(bar_KV, 0);
+            mbar_wait(&bar_in_full[0], 0);
+            tc_fence_after();
+            M1(0); M2(0);
+            for (int i = 0; i < n_q; ++i) {
+                const int b = i & 1, s = i % NS;
+                if (i + 1 < n_q) {
+                    mbar_wait(&bar_in_full[(i + 1) % NS], ((i + 1) / NS) & 1);
+                    tc_fence_after();
+                    M1(i + 1);
+                }
+                mbar_wait(&bar_P[b], (i >> 1) & 1);
+                tc_fence_after();
+                mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, i > 0);          // M3: dV += P^T dO_i
+                mbar_wait(bar_dS, i & 1);
+                tc_fence_after();
+                mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
+                umma_commit(&bar_in_empty[s]);
+                if (i + 1 < n_q) M2(i + 1);
+                mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
+                tc_fence_after();
+                {                                                                       // M5: dQ_i^T = K^T dS
+                    const uint64_t ad = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
+                    const uint64_t bd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
+#pragma unroll
+                    for (int kk = 0; kk < BN / 16; ++kk)
+                        umma_f16_ss(tmem + TM_DQ, sdesc_advance(ad, kk * 2048), sdesc_advance(bd, kk * 2048), idesc_dq, kk > 0);
+                }
+                umma_commit(bar_dQ_full);
+            }
+            umma_commit(bar_done);
+        }
+    } else if (warp >= 4 && warp < 12) {
+        const int w = (warp - 4) >> 2;
+        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_q, scale_log2, scale);
+        mbar_wait(bar_done, 0);
+        tc_fence_after();
+        bwd_epilogue(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
+    } else if (warp >= 12) {
+        bwd_drain_role(tmem, smem, bar_dQ_full, bar_dQ_empty, &tmdQ, n_q, bh);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+// ------------------------------------------------------------------------------------ host side
+// L2p[bh][q] = L * log2(e), Dp[bh][q] = D, both padded to a multiple of 64 rows per slab with
+// (+inf, 0): a padded query row then has P = exp2(0 - inf) = 0 and dS = 0, so ragged Nq needs no masks.
+__global__ void __launch_bounds__(256)
+pad_stats_kernel(const float* __restrict__ L, const float* __restrict__ D, float* __restrict__ L2p, float* __restrict__ Dp,
+                 int Nq, int Nq_pad, size_t total)
+{
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t bh = idx / Nq_pad;
+    const int q = (int)(idx - bh * Nq_pad);
+    if (q < Nq) { L2p[idx] = L[bh * Nq + q] * 1.4426950408889634f; Dp[idx] = D[bh * Nq + q]; }
+    else { L2p[idx] = INFINITY; Dp[idx] = 0.0f; }
+}
+
+__global__ void __launch_bounds__(256)
+cast_dq_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, size_t n4)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(acc)[i];
+        uint2 o;
+        o.x = pack_bf16x2(a.x, a.y);
+        o.y = pack_bf16x2(a.z, a.w);
+        reinterpret_cast<uint2*>(out)[i] = o;
+    }
+}
+
+static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv)
+{
+    return dtype == B200_DTYPE_BF16 && d == 128 && Nq >= 1 && Nkv >= 1;
+}
+
+size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
+{
+    (void)Nkv; (void)dtype;
+    const size_t Nq_pad = (size_t)(Nq + 63) / 64 * 64;
+    return 2 * al256((size_t)BH * Nq_pad * sizeof(float)) + al256((size_t)BH * Nq * d * sizeof(float));
+}
+
+int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* Dvec,
+           void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
+           void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    using namespace bwd;
+    const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
+    if ((align & 15) != 0 || BH > 65535)
+        return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
+    if (ws_bytes < tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype)) return B200_ERR_WORKSPACE;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        attr_set = true;
+    }
+    const int Nq_pad = (Nq + 63) / 64 * 64;
+    uint8_t* p = reinterpret_cast<uint8_t*>(ws);
+    float* L2p = reinterpret_cast<float*>(p); p += al256((size_t)BH * Nq_pad * sizeof(float));
+    float* Dp = reinterpret_cast<float*>(p);  p += al256((size_t)BH * Nq_pad * sizeof(float));
+    float* dQacc = reinterpret_cast<float*>(p);
+    const size_t n_dq = (size_t)BH * Nq * D;
+
+    const size_t total = (size_t)BH * Nq_pad;
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
+
+    CUtensorMap tmQ, tmK, tmV, tmdO, tmdQ, tmdK, tmdV;
+    const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, D, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, D, BM, 64) ||
+        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, D, BN, 64) ||
+        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64) ||
+        make_tmap_3d(&tmdQ, dQacc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, BH, Nq, D, BM, D, CU_TENSOR_MAP_SWIZZLE_NONE))
+        return B200_ERR_CUDA;
+    dim3 grid((Nkv + BN - 1) / BN, BH);
+    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, tmdQ, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
+                                            scale * 1.4426950408889634f, scale);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
+    if (cgrid > 148u * 8) cgrid = 148u * 8;
+    cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
+}  // namespace b200

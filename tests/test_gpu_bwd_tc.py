@@ -1,0 +1,67 @@
+"""GPU parity of the tcgen05 backward (through the C-ABI) against the oracle's O(N^2 d) backward
+(itself pinned against the reference's Jacobian form in tests/test_oracle.py).
+Tolerance (north_star, bf16 inputs): max-abs <= 2e-2 and rel-L2 <= 1e-2."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import cuda_flashattention_b200 as fa
+from gpu_util import dev, host, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(Nq, Nkv, d, seed, qscale=1.0, B=1, H=1):
+    rng = np.random.default_rng(seed)
+    shp_q, shp_k = (B, H, Nq, d), (B, H, Nkv, d)
+    q = dev(qscale * rng.standard_normal(shp_q).astype(np.float32), torch.bfloat16)
+    k = dev(rng.standard_normal(shp_k).astype(np.float32), torch.bfloat16)
+    v = dev(rng.standard_normal(shp_k).astype(np.float32), torch.bfloat16)
+    do = dev(rng.standard_normal(shp_q).astype(np.float32), torch.bfloat16)
+    assert fa.uses_tensor_cores(torch.bfloat16, d, Nq, Nkv, backward=True)
+    O, L = fa.flash_attention_2_forward(q, k, v, 0.0)
+    dQ, dK, dV = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0)
+    worst = {}
+    for b in range(B):
+        for h in range(H):
+            ref = oracle.backward(host(q[b, h]), host(k[b, h]), host(v[b, h]), host(do[b, h]), 0.0)
+            for name, got, want in zip(("dQ", "dK", "dV"), (dQ, dK, dV), ref):
+                g = host(got[b, h])
+                e = (float(np.abs(g - want).max()), rel_l2(g, want))
+                worst[name] = max(worst.get(name, (0, 0)), e)
+    print(Nq, Nkv, worst)
+    for name, (mx, rl) in worst.items():
+        assert mx <= 2e-2 * max(1.0, float(np.abs(want).max())), (name, mx)
+        assert rl <= 1e-2, (name, rl)
+
+
+@pytest.mark.parametrize("N", [64, 128, 256, 1000, 2048])
+def test_bwd_square(N):
+    _check(N, N, 128, N)
+
+
+def test_bwd_cross_lengths_batched():
+    _check(200, 333, 128, 5, B=2, H=3)
+
+
+def test_bwd_peaky():
+    _check(512, 512, 128, 44, qscale=3.0)
+
+
+def test_bwd_large_against_generic():
+    rng = np.random.default_rng(3)
+    B, H, N, d = 1, 4, 4096, 128
+    q, k, v, do = [dev(rng.standard_normal((B, H, N, d)).astype(np.float32), torch.bfloat16) for _ in range(4)]
+    O, L = fa.flash_attention_2_forward(q, k, v, 0.0)
+    got = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0)
+    fa.lib.b200_debug_force_generic(1)
+    try:
+        ref = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0)
+    finally:
+        fa.lib.b200_debug_force_generic(0)
+    for name, a, b in zip(("dQ", "dK", "dV"), got, ref):
+        err = (a.float() - b.float()).abs().max().item()
+        rl = ((a.float() - b.float()).norm() / b.float().norm()).item()
+        print(name, err, rl)
+        assert err <= 2e-2 and rl <= 1e-2
