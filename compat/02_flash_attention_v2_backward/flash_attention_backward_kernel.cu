@@ -1,4 +1,4 @@
-// Source-compat shim: same file name as the reference kernel file the drivers #include textually;
+// Source-compat shim: same path as the reference kernel file its driver #includes textually;
 // the kernels themselves live in libb200attn.so.  See compat/b200_compat.h.
 #pragma once
 #include "../util/cuda_helper.h"

@@ -1,0 +1,6 @@
+// Source-compat shim for src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu (see compat/b200_compat.h).
+#pragma once
+#include "../../util/nccl_utils.h"
+#include "../../util/cuda_helper.h"
+#include "../../util/attention_helper.h"
+#include "../../b200_compat.h"
