@@ -2,7 +2,6 @@
 # Runs the reference's own (unmodified) driver programs, linked against libb200attn.so, on the GPU box.
 # 04_ring runs as 1 rank by default; set NRANKS=2 (needs 2 GPUs) for the real ring.
 cd "$(dirname "$0")/_dropin" || exit 1
-export LD_LIBRARY_PATH=$(dirname $(python -c "import nvidia.nccl, os; print(os.path.join(list(nvidia.nccl.__path__)[0], 'lib', 'x'))" 2>/dev/null):${LD_LIBRARY_PATH}
 rc=0
 for p in 01_fa1 02_fwd 02_bwd 03_1gpu; do
   echo "=== $p"; timeout 120 ./$p > $p.log 2>&1; echo "exit $?"; grep -E "PASS|FAIL|Pass|pass|match|Max diff|max_diff|Max difference" $p.log | tail -12
