@@ -128,6 +128,12 @@ const char* b200_strerror(int s)
 int b200_last_cuda_error(void) { return g_last_cuda_error; }
 int b200_version(void) { return 100; }
 unsigned long long b200_debug_launch_count(void) { return g_launches; }
+#ifdef B200_TRACE
+}
+namespace b200 { int fwd_trace_read(long long* out, int n); }
+extern "C" {
+__attribute__((visibility("default"))) int b200_debug_trace_read(long long* out, int n) { return b200::fwd_trace_read(out, n); }
+#endif
 int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generic = on ? 1 : 0; return old; }
 
 int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }

@@ -194,7 +194,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint64_t* bar_done = bar_dQ_empty + 1;       // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
     const int bh = blockIdx.y, kv0 = blockIdx.x * BN;
     const int n_q = (Nq + BM - 1) / BM;
 
@@ -216,7 +216,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 
     if (warp == 0) {
         // ================================ TMA producer ================================
-        if (lane == 0) {
+        if (elect_one()) {
             mbar_expect_tx(bar_KV, 2 * KV_TILE);
             for (int b = 0; b < 2; ++b) {
                 tma_load_3d(smem + OFF_K + b * KV_BOX, &tmK, bar_KV, b * 64, kv0, bh, kEvictFirst);
@@ -238,7 +238,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==================================
-        if (lane == 0) {
+        if (elect_one()) {
             constexpr uint32_t idesc_ss = make_idesc(kFmtBF16, 128, BM, false, false);   // M1, M2
             constexpr uint32_t idesc_ts = make_idesc(kFmtBF16, 128, D, false, true);     // M3, M4
             constexpr uint32_t idesc_dq = make_idesc(kFmtBF16, 128, BM, true, true);     // M5

@@ -20,10 +20,26 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
+#include <type_traits>
+#include <stdlib.h>
 
 namespace b200 {
 
-template <typename Elem_, int D_, int NT_, int BC_>
+// Optional in-kernel event trace (build with EXTRA=-DB200_TRACE): CTA (0,0) records clock64() at the
+// hand-off points of iterations 16..23; read back with b200_debug_trace_read.  Compiled out otherwise.
+#ifdef B200_TRACE
+__device__ long long g_trace[3 * 8 * 8];
+#define B200_TR(role, j, ev)                                                                       \
+    do { if (blockIdx.x == 0 && blockIdx.y == 0 && (j) >= 16 && (j) < 24 && (threadIdx.x & 31) == 0 && \
+             ((role) == 2 || ((threadIdx.x >> 5) & 3) == 0))                                        \
+            g_trace[((role) * 8 + ((j) - 16)) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define B200_TR(role, j, ev) do {} while (0)
+#endif
+
+// POLY = how many of every 16 (score, score) pairs get their exp2 from the FMA-pipe polynomial
+// instead of the MUFU (bf16 only); SPLITP = P is published to the MMA warp in two halves.
+template <typename Elem_, int D_, int NT_, int BC_, int POLY_ = 0, bool SPLITP_ = true>
 struct FwdCfg {
     using Elem = Elem_;
     static constexpr int EB = sizeof(Elem);
@@ -35,14 +51,19 @@ struct FwdCfg {
     static constexpr int Q_BOX = BR * 128, KV_BOX = BC * 128;
     static constexpr int Q_TILE = BOXES * Q_BOX, KV_TILE = BOXES * KV_BOX;
     static constexpr int THREADS = 128 + NT * 128;
-    static constexpr int NBARS = NT * 4 + STAGES * 4;
+    static constexpr int POLY = POLY_;
+    static constexpr bool SPLITP = SPLITP_;
+    static constexpr int NBARS = NT * 5 + STAGES * 4;
+    static constexpr int REGS_CTRL = 64, REGS_SOFTMAX = 216;   // setmaxnreg targets (warps 0-3 / softmax)
     static constexpr int SMEM = 1024 + NT * Q_TILE + 2 * STAGES * KV_TILE + NBARS * 8 + 16;
     static constexpr int PCOLS_PER_CHUNK = kF32 ? 32 : 16;   // TMEM columns written per 32 P values
     // V is the MN-major B operand of O += P V.  bf16: plain 128B swizzle.  tf32: the hardware only
     // accepts the 32-byte-atom 128B swizzle for MN-major operands (4-row pattern, SBO = 512).
     static constexpr uint32_t V_LAYOUT = kF32 ? 1u : 2u;
     static constexpr uint32_t V_SBO = kF32 ? 512u : 1024u;
-    static_assert(D % CPB == 0 && BC % 32 == 0 && BC <= 128 && D <= 128, "tile shape");
+    static_assert(D % CPB == 0 && BC % 64 == 0 && BC <= 128 && D <= 128, "tile shape");
+    static_assert(POLY == 0 || !kF32, "the polynomial exp2 is only accurate enough for bf16 P");
+    static_assert(128 * REGS_CTRL + 256 * REGS_SOFTMAX <= 65536, "register file");
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
 };
 
@@ -68,9 +89,10 @@ constexpr float kRescaleThreshold = 8.0f;
 
 // One softmax warpgroup (128 threads) serving query tile t.  Thread r owns query row r of the tile.
 template <class C>
-__device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, uint64_t* bar_S, uint64_t* bar_P,
-                                             uint64_t* bar_O, const CUtensorMap* tmO, float* __restrict__ Lout,
-                                             int Nq, int Nkv, int nkv, int q0, int bh, float scale_log2)
+__device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, uint64_t* bar_S, uint64_t* bar_Pa,
+                                             uint64_t* bar_Pb, uint64_t* bar_O, const CUtensorMap* tmO,
+                                             float* __restrict__ Lout, int Nq, int Nkv, int nkv, int q0, int bh,
+                                             float scale_log2)
 {
     constexpr int BC = C::BC, D = C::D;
     const int wg_thread = threadIdx.x & 127;                       // == TMEM lane == row within the tile
@@ -79,22 +101,34 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     const uint32_t tS = tmem + 128 * t + lane_base;                // S_t and (aliased) P_t
     const uint32_t tO = tmem + 256 + 128 * t + lane_base;
     const int tail = Nkv - (nkv - 1) * BC;                         // valid columns in the last K/V tile
+    const uint64_t scale2 = f2_pack(scale_log2, scale_log2);
 
     float m = -INFINITY, l = 0.0f;                                 // m in log2 units (already scaled)
-    for (int j = 0; j < nkv; ++j) {
+
+    // one K/V tile: S_t(j) -> (m, l) update -> P_t(j).  kMasked = the ragged last tile.
+    auto step = [&](auto masked_tag, const int j) {
+        constexpr bool kMasked = decltype(masked_tag)::value;
         mbar_wait(bar_S, j & 1);
         tc_fence_after();
+        B200_TR(t, j, 0);
         uint32_t s[BC];
 #pragma unroll
         for (int c = 0; c < BC / 32; ++c) B200_TMEM_LD_32(tS + 32 * c, s + 32 * c);
         tmem_wait_ld();
-        if (j == nkv - 1 && tail < BC) {
+        B200_TR(t, j, 1);
+        if constexpr (kMasked) {
 #pragma unroll
             for (int i = 0; i < BC; ++i) if (i >= tail) s[i] = 0xff800000u;      // -inf
         }
-        float mx = __uint_as_float(s[0]);
+        // row max: four independent chains (FMNMX3) so the dependent depth is BC/8, not BC/2
+        float mq[4];
 #pragma unroll
-        for (int i = 1; i < BC; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+        for (int q = 0; q < 4; ++q) {
+            mq[q] = __uint_as_float(s[q]);
+#pragma unroll
+            for (int i = 4 + q; i < BC; i += 4) mq[q] = fmaxf(mq[q], __uint_as_float(s[i]));
+        }
+        const float mx = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
         const float m_new = fmaxf(m, mx * scale_log2);
         const bool need = (m_new - m) > kRescaleThreshold;
         float alpha = 1.0f;
@@ -111,33 +145,53 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
                 B200_TMEM_ST_32(tO + 32 * c, o);
             }
         }
-        const float neg_m = -m;
-        float lsum = 0.0f;
+        B200_TR(t, j, 2);
+        const uint64_t neg_m2 = f2_pack(-m, -m);
+        uint64_t acc[4] = {0ull, 0ull, 0ull, 0ull};                // packed partial row sums (8 independent adders)
 #pragma unroll
         for (int c = 0; c < BC / 32; ++c) {
-            float p[32];
+            uint32_t r[32];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                p[i] = fast_exp2(fmaf(__uint_as_float(s[32 * c + i]), scale_log2, neg_m));
-                lsum += p[i];
+            for (int i = 0; i < 16; ++i) {
+                const uint64_t x = f2_fma(f2_pack(__uint_as_float(s[32 * c + 2 * i]), __uint_as_float(s[32 * c + 2 * i + 1])), scale2, neg_m2);
+                float p0, p1;
+                // spread the polynomial pairs evenly through the chunk so MUFU and FMA work interleave
+                const bool poly = !kMasked && C::POLY > 0 && ((i * C::POLY) % 16 < C::POLY);
+                if (poly) {
+                    exp2_poly2(x, p0, p1);
+                } else {
+                    float x0, x1;
+                    f2_unpack(x, x0, x1);
+                    p0 = fast_exp2(x0);
+                    p1 = fast_exp2(x1);
+                }
+                acc[i & 3] = f2_add(acc[i & 3], f2_pack(p0, p1));
+                if constexpr (C::kF32) { r[2 * i] = cvt_tf32(p0); r[2 * i + 1] = cvt_tf32(p1); }
+                else r[i] = pack_bf16x2(p0, p1);
             }
-            if constexpr (C::kF32) {
-                uint32_t r[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) r[i] = cvt_tf32(p[i]);
-                B200_TMEM_ST_32(tS + 32 * c, r);
-            } else {
-                uint32_t r[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) r[i] = pack_bf16x2(p[2 * i], p[2 * i + 1]);
-                B200_TMEM_ST_16(tS + 16 * c, r);
+            if constexpr (C::kF32) B200_TMEM_ST_32(tS + 32 * c, r); else B200_TMEM_ST_16(tS + 16 * c, r);
+            if (C::SPLITP && c == BC / 64 - 1) {                   // first half of P is in TMEM: PV can start
+                tmem_wait_st();
+                tc_fence_before();
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) mbar_arrive(bar_Pa);
+                B200_TR(t, j, 3);
             }
         }
-        l = l * alpha + lsum;
+        float a0, a1, a2, a3;
+        f2_unpack(f2_add(acc[0], acc[1]), a0, a1);
+        f2_unpack(f2_add(acc[2], acc[3]), a2, a3);
+        l = fmaf(l, alpha, (a0 + a1) + (a2 + a3));
+        B200_TR(t, j, 4);
         tmem_wait_st();
         tc_fence_before();
-        mbar_arrive(bar_P);
-    }
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(bar_Pb);
+        B200_TR(t, j, 5);
+    };
+
+    for (int j = 0; j < nkv - 1; ++j) step(std::false_type{}, j);
+    step(std::true_type{}, nkv - 1);                               // (a full last tile masks nothing)
 
     // ---- epilogue: O_t / l -> smem (reusing the Q tile, 128B-swizzled) -> TMA store; LSE -> global
     mbar_wait(bar_O, 0);
@@ -202,22 +256,23 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ST * C::KV_TILE);
     uint64_t* bar_Q = bars;                 // [NT]  Q tile landed
     uint64_t* bar_S = bar_Q + NT;           // [NT]  S_t(j) complete in TMEM
-    uint64_t* bar_P = bar_S + NT;           // [NT]  P_t(j) written (128 arrivals)
-    uint64_t* bar_O = bar_P + NT;           // [NT]  last PV of tile t complete
+    uint64_t* bar_Pa = bar_S + NT;          // [NT]  first half of P_t(j) written (one arrival per softmax warp)
+    uint64_t* bar_Pb = bar_Pa + NT;         // [NT]  all of P_t(j) written
+    uint64_t* bar_O = bar_Pb + NT;          // [NT]  last PV of tile t complete
     uint64_t* bar_Kf = bar_O + NT;          // [ST]
     uint64_t* bar_Ke = bar_Kf + ST;
     uint64_t* bar_Vf = bar_Ke + ST;
     uint64_t* bar_Ve = bar_Vf + ST;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_Ve + ST);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
     const int bh = blockIdx.y;
     const int q0 = blockIdx.x * (NT * 128);
     const int ntiles = min(NT, (Nq - q0 + 127) / 128);
     const int nkv = (Nkv + BC - 1) / BC;
 
     if (threadIdx.x == 0) {
-        for (int t = 0; t < NT; ++t) { mbar_init(&bar_Q[t], 1); mbar_init(&bar_S[t], 1); mbar_init(&bar_P[t], 128); mbar_init(&bar_O[t], 1); }
+        for (int t = 0; t < NT; ++t) { mbar_init(&bar_Q[t], 1); mbar_init(&bar_S[t], 1); mbar_init(&bar_Pa[t], 4); mbar_init(&bar_Pb[t], 4); mbar_init(&bar_O[t], 1); }
         for (int s = 0; s < ST; ++s) { mbar_init(&bar_Kf[s], 1); mbar_init(&bar_Ke[s], 1); mbar_init(&bar_Vf[s], 1); mbar_init(&bar_Ve[s], 1); }
         fence_mbar_init();
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
@@ -228,9 +283,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
+    // NT == 2 runs 384 threads: the control warps hand registers to the softmax warps (setmaxnreg is
+    // issued inside each role's branch -- ptxas only honours it for the code it dominates).
     if (warp == 0) {
         // ================================ TMA producer ================================
-        if (lane == 0) {
+        if constexpr (NT == 2) reg_dec<C::REGS_CTRL>();
+        if (elect_one()) {
             for (int t = 0; t < ntiles; ++t) {
                 mbar_expect_tx(&bar_Q[t], C::Q_TILE);
                 for (int b = 0; b < C::BOXES; ++b)
@@ -251,7 +309,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==================================
-        if (lane == 0) {
+        if constexpr (NT == 2) reg_dec<C::REGS_CTRL>();
+        if (elect_one()) {
             constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : kFmtBF16;
             constexpr uint32_t idesc_S = make_idesc(fmt, 128, BC, false, false);
             constexpr uint32_t idesc_PV = make_idesc(fmt, 128, D, false, true);
@@ -269,13 +328,16 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 }
                 umma_commit(&bar_S[t]);
             };
-            auto issue_PV = [&](int t, int j) {
+            auto issue_PV = [&](int t, int j, int half) {       // half 0 / 1 = first / second BC/2 columns of P
                 const int s = j % ST;
                 const uint64_t vd = make_sdesc(v_base + s * C::KV_TILE, C::KV_BOX, C::V_SBO, C::V_LAYOUT);
+                constexpr int KH = BC / C::KPER / 2;
 #pragma unroll
-                for (int kk = 0; kk < BC / C::KPER; ++kk)
+                for (int k2 = 0; k2 < KH; ++k2) {
+                    const int kk = half * KH + k2;
                     umma_ts<C::kF32>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
                                      sdesc_advance(vd, kk * C::KPER * 128), idesc_PV, (j > 0 || kk > 0));
+                }
             };
 
             mbar_wait(&bar_Kf[0], 0);
@@ -290,9 +352,16 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 mbar_wait(&bar_Vf[s], (j / ST) & 1);
                 if (j + 1 < nkv) mbar_wait(&bar_Kf[(j + 1) % ST], ((j + 1) / ST) & 1);
                 for (int t = 0; t < ntiles; ++t) {
-                    mbar_wait(&bar_P[t], j & 1);
+                    if (C::SPLITP) {
+                        mbar_wait(&bar_Pa[t], j & 1);
+                        tc_fence_after();
+                        issue_PV(t, j, 0);
+                    }
+                    mbar_wait(&bar_Pb[t], j & 1);
                     tc_fence_after();
-                    issue_PV(t, j);
+                    B200_TR(2, j, 2 * t);
+                    if (!C::SPLITP) issue_PV(t, j, 0);
+                    issue_PV(t, j, 1);
                     if (t == ntiles - 1) umma_commit(&bar_Ve[s]);
                     if (j + 1 < nkv) {
                         issue_S(t, j + 1);
@@ -300,13 +369,17 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                     } else {
                         umma_commit(&bar_O[t]);
                     }
+                    B200_TR(2, j, 2 * t + 1);
                 }
             }
         }
-    } else if (warp >= 4) {
+    } else if (warp < 4) {
+        if constexpr (NT == 2) reg_dec<C::REGS_CTRL>();
+    } else {
         // ================================ softmax warpgroups ==========================
+        if constexpr (NT == 2) reg_inc<C::REGS_SOFTMAX>();
         const int t = (warp - 4) >> 2;
-        if (t < ntiles) softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_P[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv, q0, bh, scale_log2);
+        if (t < ntiles) softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv, q0, bh, scale_log2);
     }
 
     tc_fence_before();
@@ -344,6 +417,15 @@ static int launch_fwd(const void* Q, const void* K, const void* V, void* O, floa
     return B200_OK;
 }
 
+#ifdef B200_TRACE
+int fwd_trace_read(long long* out, int n)
+{
+    if (n > 3 * 8 * 8) n = 3 * 8 * 8;
+    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_trace, n * sizeof(long long)));
+    return n;
+}
+#endif
+
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
 {
     if (Nq < 1 || Nkv < 1) return false;
@@ -358,8 +440,17 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
     if ((align & 15) != 0 || !(scale > 0.0f))      // TMA needs 16-byte bases; max(S)*scale needs scale > 0
         return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
     if (dtype == B200_DTYPE_BF16) {
-        if (d == 128) return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
-        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+        static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
+        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 61; }
+        if (d == 128) {
+            switch (variant) {
+#define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+                B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
+#undef B200_V
+                default: return B200_ERR_UNSUPPORTED;
+            }
+        }
+        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 6, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
     }
     if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
     return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);

@@ -258,4 +258,51 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// ------------------------------------------------------------------ packed fp32x2 arithmetic (sm_100: FFMA2 / FADD2 / FMUL2)
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// 2^x for a pair of fp32 values on the FMA pipe instead of the MUFU: x = n + f with n = round(x),
+// f in [-0.5, 0.5]; 2^f by a degree-3 minimax polynomial (max relative error 7.5e-5, far below the
+// bf16 rounding the result goes through), 2^n by adding n to the exponent field.  x is clamped at
+// -125 so the exponent arithmetic cannot wrap (2^-125 is zero for every purpose here).
+__device__ __forceinline__ void exp2_poly2(uint64_t x, float& p_lo, float& p_hi) {
+    float lo, hi;
+    f2_unpack(x, lo, hi);
+    lo = fmaxf(lo, -125.0f);
+    hi = fmaxf(hi, -125.0f);
+    x = f2_pack(lo, hi);
+    const uint64_t t = f2_add(x, f2_pack(12582912.0f, 12582912.0f));            // 1.5 * 2^23: low mantissa bits = n
+    const uint64_t n = f2_add(t, f2_pack(-12582912.0f, -12582912.0f));
+    const uint64_t f = f2_fma(n, f2_pack(-1.0f, -1.0f), x);
+    uint64_t p = f2_fma(f2_pack(0.05517164617776871f, 0.05517164617776871f), f, f2_pack(0.2426111251115799f, 0.2426111251115799f));
+    p = f2_fma(p, f, f2_pack(0.6932609677314758f, 0.6932609677314758f));
+    p = f2_fma(p, f, f2_pack(0.9999280571937561f, 0.9999280571937561f));
+    float tl, th, pl, ph;
+    f2_unpack(t, tl, th);
+    f2_unpack(p, pl, ph);
+    p_lo = __uint_as_float((__float_as_uint(tl) << 23) + __float_as_uint(pl));
+    p_hi = __uint_as_float((__float_as_uint(th) << 23) + __float_as_uint(ph));
+}
+
 }  // namespace b200

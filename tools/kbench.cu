@@ -1,0 +1,114 @@
+// kbench.cu -- native micro-harness for the C-ABI (no Python/torch start-up): device-resident
+// N(0,1) inputs, CUDA-event timing of b200_fa2_fwd / b200_fa2_bwd, optional in-kernel trace dump
+// (library built with EXTRA=-DB200_TRACE).  Not the contract bench (that is bench.py).
+//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace]
+//   env B200ATTN_LIB = path of the shared object (default: cuda_flashattention_b200/libb200attn.so)
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include <algorithm>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "%s:%d %s\n", __FILE__, __LINE__, cudaGetErrorString(e_)); exit(2); } } while (0)
+
+__device__ __forceinline__ uint32_t mix(uint64_t x) {
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+    return (uint32_t)x;
+}
+template <typename T>
+__global__ void fill_normal(T* p, size_t n, uint64_t seed, float sigma) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const float u1 = (mix(seed * 0x9E3779B97F4A7C15ull + 2 * i) + 1.0f) * (1.0f / 4294967808.0f);
+        const float u2 = mix(seed * 0x9E3779B97F4A7C15ull + 2 * i + 1) * (1.0f / 4294967296.0f);
+        const float v = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2) * sigma;
+        if constexpr (sizeof(T) == 2) p[i] = __float2bfloat16(v); else p[i] = v;
+    }
+}
+
+typedef int (*fwd_t)(const void*, const void*, const void*, void*, float*, int, int, int, int, int, float, int, cudaStream_t);
+typedef int (*bwd_t)(const void*, const void*, const void*, const void*, const float*, const void*, void*, void*, void*,
+                     int, int, int, int, int, float, int, void*, size_t, cudaStream_t);
+typedef size_t (*ws_t)(int, int, int, int, int, int);
+typedef int (*trace_t)(long long*, int);
+
+int main(int argc, char** argv)
+{
+    if (argc < 7) { fprintf(stderr, "usage: kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace]\n"); return 1; }
+    const char* mode = argv[1];
+    const int B = atoi(argv[2]), H = atoi(argv[3]), N = atoi(argv[4]), d = atoi(argv[5]);
+    const bool f32 = strcmp(argv[6], "f32") == 0;
+    int iters = 10; bool trace = false;
+    for (int i = 7; i < argc; ++i) { if (!strcmp(argv[i], "--trace")) trace = true; else iters = atoi(argv[i]); }
+    const char* path = getenv("B200ATTN_LIB");
+    if (!path) path = "cuda_flashattention_b200/libb200attn.so";
+    void* h = dlopen(path, RTLD_NOW);
+    if (!h) { fprintf(stderr, "dlopen %s: %s\n", path, dlerror()); return 2; }
+    fwd_t fwd = (fwd_t)dlsym(h, "b200_fa2_fwd");
+    bwd_t bwd = (bwd_t)dlsym(h, "b200_fa2_bwd");
+    ws_t wsb = (ws_t)dlsym(h, "b200_fa2_bwd_workspace_bytes");
+    trace_t tr = (trace_t)dlsym(h, "b200_debug_trace_read");
+    if (!fwd || !bwd || !wsb) { fprintf(stderr, "missing symbols\n"); return 2; }
+
+    const size_t n = (size_t)B * H * N * d, eb = f32 ? 4 : 2;
+    void *Q, *K, *V, *O, *dO, *dQ, *dK, *dV, *ws; float* L;
+    CK(cudaMalloc(&Q, n * eb)); CK(cudaMalloc(&K, n * eb)); CK(cudaMalloc(&V, n * eb)); CK(cudaMalloc(&O, n * eb));
+    CK(cudaMalloc(&dO, n * eb)); CK(cudaMalloc(&dQ, n * eb)); CK(cudaMalloc(&dK, n * eb)); CK(cudaMalloc(&dV, n * eb));
+    CK(cudaMalloc(&L, (size_t)B * H * N * 4));
+    const int dt = f32 ? 1 : 0;
+    const size_t wsn = wsb(B, H, N, N, d, dt);
+    CK(cudaMalloc(&ws, wsn ? wsn : 16));
+    void* bufs[4] = {Q, K, V, dO};
+    for (int i = 0; i < 4; ++i) {
+        if (f32) fill_normal<float><<<148 * 8, 256>>>((float*)bufs[i], n, 1234 + i, 1.0f);
+        else fill_normal<__nv_bfloat16><<<148 * 8, 256>>>((__nv_bfloat16*)bufs[i], n, 1234 + i, 1.0f);
+    }
+    CK(cudaDeviceSynchronize());
+    const bool do_f = strcmp(mode, "bwd") != 0, do_b = strcmp(mode, "fwd") != 0;
+    auto run_f = [&]() { int s = fwd(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 0); if (s) { fprintf(stderr, "fwd status %d\n", s); exit(3); } };
+    auto run_b = [&]() { int s = bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, ws, wsn, 0); if (s) { fprintf(stderr, "bwd status %d\n", s); exit(3); } };
+    run_f();
+    for (int i = 0; i < 3; ++i) { if (do_f) run_f(); if (do_b) run_b(); }
+    CK(cudaDeviceSynchronize());
+    std::vector<float> tf, tb;
+    cudaEvent_t e0, e1, e2;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
+    for (int i = 0; i < iters; ++i) {
+        CK(cudaEventRecord(e0));
+        if (do_f) run_f();
+        CK(cudaEventRecord(e1));
+        if (do_b) run_b();
+        CK(cudaEventRecord(e2));
+        CK(cudaEventSynchronize(e2));
+        float a, b;
+        CK(cudaEventElapsedTime(&a, e0, e1)); CK(cudaEventElapsedTime(&b, e1, e2));
+        tf.push_back(a); tb.push_back(b);
+    }
+    auto med = [](std::vector<float> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
+    auto mn = [](std::vector<float> v) { return *std::min_element(v.begin(), v.end()); };
+    const double ff = 4.0 * B * H * (double)N * N * d, fb = 10.0 * B * H * (double)N * N * d;
+    printf("B=%d H=%d N=%d d=%d %s:", B, H, N, d, f32 ? "f32" : "bf16");
+    if (do_f) printf("  fwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tf), ff / med(tf) / 1e9, mn(tf), ff / mn(tf) / 1e9);
+    if (do_b) printf("  bwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tb), fb / med(tb) / 1e9, mn(tb), fb / mn(tb) / 1e9);
+    printf("\n");
+    if (trace) {
+        if (!tr) { fprintf(stderr, "library was not built with -DB200_TRACE\n"); return 4; }
+        long long t[3 * 8 * 8];
+        tr(t, 3 * 8 * 8);
+        const long long t0 = t[0];
+        const char* names[3] = {"softmax0", "softmax1", "mma"};
+        for (int r = 0; r < 3; ++r)
+            for (int j = 0; j < 8; ++j) {
+                printf("%-8s j=%2d:", names[r], 16 + j);
+                for (int e = 0; e < 6; ++e) printf(" %7lld", t[(r * 8 + j) * 8 + e] ? t[(r * 8 + j) * 8 + e] - t0 : -1);
+                printf("\n");
+            }
+    }
+    return 0;
+}
