@@ -120,74 +120,86 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
 #pragma unroll
             for (int i = 0; i < BC; ++i) if (i >= tail) s[i] = 0xff800000u;      // -inf
         }
-        // row max: four independent chains (FMNMX3) so the dependent depth is BC/8, not BC/2
+        // P for chunks [32 c0, 32 c1) of the row with the running max m; partial row sums into acc
+        uint64_t acc[4];
+        auto exp_chunks = [&](const int c0, const int c1, const float m_use) {
+            const uint64_t neg_m2 = f2_pack(-m_use, -m_use);
+#pragma unroll
+            for (int c = c0; c < c1; ++c) {
+                uint32_t r[32];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const uint64_t x = f2_fma(f2_pack(__uint_as_float(s[32 * c + 2 * i]), __uint_as_float(s[32 * c + 2 * i + 1])), scale2, neg_m2);
+                    float p0, p1;
+                    // spread the polynomial pairs evenly through the chunk so MUFU and FMA work interleave
+                    const bool poly = !kMasked && C::POLY > 0 && ((i * C::POLY) % 16 < C::POLY);
+                    if (poly) {
+                        exp2_poly2(x, p0, p1);
+                    } else {
+                        float x0, x1;
+                        f2_unpack(x, x0, x1);
+                        p0 = fast_exp2(x0);
+                        p1 = fast_exp2(x1);
+                    }
+                    if (c == 0 && i < 4) acc[i] = f2_pack(p0, p1); else acc[i & 3] = f2_add(acc[i & 3], f2_pack(p0, p1));
+                    if constexpr (C::kF32) { r[2 * i] = cvt_tf32(p0); r[2 * i + 1] = cvt_tf32(p1); }
+                    else r[i] = pack_bf16x2(p0, p1);
+                }
+                if constexpr (C::kF32) B200_TMEM_ST_32(tS + 32 * c, r); else B200_TMEM_ST_16(tS + 16 * c, r);
+            }
+        };
+        // Speculate: the first half of P is computed with the running max as it stands, while the row
+        // max of this tile (independent ALU work on the same registers) is still being reduced.  The
+        // lazy-rescale rule makes the speculation right almost always; when the max does grow by more
+        // than the threshold (always at j = 0) the half is simply recomputed with the new max.
+        exp_chunks(0, BC / 64, m);
+        // row max: four independent chains over contiguous quarters; each FMNMX3 takes an (even, odd)
+        // register pair so its three sources never collide on a register bank
         float mq[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            mq[q] = __uint_as_float(s[q]);
+            constexpr int QW = BC / 4;
+            mq[q] = fmaxf(__uint_as_float(s[QW * q]), __uint_as_float(s[QW * q + 1]));
 #pragma unroll
-            for (int i = 4 + q; i < BC; i += 4) mq[q] = fmaxf(mq[q], __uint_as_float(s[i]));
+            for (int i = 2; i < QW; i += 2)
+                mq[q] = fmaxf(mq[q], fmaxf(__uint_as_float(s[QW * q + i]), __uint_as_float(s[QW * q + i + 1])));
         }
         const float mx = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
         const float m_new = fmaxf(m, mx * scale_log2);
         const bool need = (m_new - m) > kRescaleThreshold;
         float alpha = 1.0f;
-        if (need) { alpha = fast_exp2(m - m_new); m = m_new; }
-        if (j > 0 && __any_sync(0xffffffffu, need)) {
-            // PV_t(j-1) is complete (bar_S(j) was committed after it), PV_t(j) not yet issued: O_t is ours.
-#pragma unroll
-            for (int c = 0; c < D / 32; ++c) {
-                uint32_t o[32];
-                B200_TMEM_LD_32(tO + 32 * c, o);
-                tmem_wait_ld();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-                B200_TMEM_ST_32(tO + 32 * c, o);
-            }
-        }
         B200_TR(t, j, 2);
-        const uint64_t neg_m2 = f2_pack(-m, -m);
-        uint64_t acc[4] = {0ull, 0ull, 0ull, 0ull};                // packed partial row sums (8 independent adders)
+        if (__any_sync(0xffffffffu, need)) {
+            if (need) { alpha = fast_exp2(m - m_new); m = m_new; }
+            if (j > 0) {
+                // PV_t(j-1) is complete (bar_S(j) was committed after it), PV_t(j) not yet issued: O_t is ours.
 #pragma unroll
-        for (int c = 0; c < BC / 32; ++c) {
-            uint32_t r[32];
+                for (int c = 0; c < D / 32; ++c) {
+                    uint32_t o[32];
+                    B200_TMEM_LD_32(tO + 32 * c, o);
+                    tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const uint64_t x = f2_fma(f2_pack(__uint_as_float(s[32 * c + 2 * i]), __uint_as_float(s[32 * c + 2 * i + 1])), scale2, neg_m2);
-                float p0, p1;
-                // spread the polynomial pairs evenly through the chunk so MUFU and FMA work interleave
-                const bool poly = !kMasked && C::POLY > 0 && ((i * C::POLY) % 16 < C::POLY);
-                if (poly) {
-                    exp2_poly2(x, p0, p1);
-                } else {
-                    float x0, x1;
-                    f2_unpack(x, x0, x1);
-                    p0 = fast_exp2(x0);
-                    p1 = fast_exp2(x1);
+                    for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    B200_TMEM_ST_32(tO + 32 * c, o);
                 }
-                acc[i & 3] = f2_add(acc[i & 3], f2_pack(p0, p1));
-                if constexpr (C::kF32) { r[2 * i] = cvt_tf32(p0); r[2 * i + 1] = cvt_tf32(p1); }
-                else r[i] = pack_bf16x2(p0, p1);
             }
-            if constexpr (C::kF32) B200_TMEM_ST_32(tS + 32 * c, r); else B200_TMEM_ST_16(tS + 16 * c, r);
-            if (C::SPLITP && c == BC / 64 - 1) {                   // first half of P is in TMEM: PV can start
-                tmem_wait_st();
-                tc_fence_before();
-                __syncwarp();
-                if ((threadIdx.x & 31) == 0) mbar_arrive(bar_Pa);
-                B200_TR(t, j, 3);
-            }
+            exp_chunks(0, BC / 64, m);                             // redo the speculated half with the new max
         }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(bar_Pa);         // first half of P is in TMEM: PV can start
+        B200_TR(t, j, 4);
+        exp_chunks(BC / 64, BC / 32, m);
         float a0, a1, a2, a3;
         f2_unpack(f2_add(acc[0], acc[1]), a0, a1);
         f2_unpack(f2_add(acc[2], acc[3]), a2, a3);
         l = fmaf(l, alpha, (a0 + a1) + (a2 + a3));
-        B200_TR(t, j, 4);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if ((threadIdx.x & 31) == 0) mbar_arrive(bar_Pb);
-        B200_TR(t, j, 5);
+        B200_TR(t, j, 7);
     };
 
     for (int j = 0; j < nkv - 1; ++j) step(std::false_type{}, j);
@@ -441,7 +453,7 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
         return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
     if (dtype == B200_DTYPE_BF16) {
         static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
-        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 61; }
+        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
         if (d == 128) {
             switch (variant) {
 #define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
@@ -450,7 +462,7 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
                 default: return B200_ERR_UNSUPPORTED;
             }
         }
-        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 6, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
     }
     if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
     return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);

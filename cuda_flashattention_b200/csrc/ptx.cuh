@@ -63,14 +63,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
 #if B200_MBAR_TIMEOUT_CYCLES
-    long long t0 = clock64();
+    // The watchdog reads the clock only once every 4096 polls: the polling loop shares issue slots
+    // with the working warps of its SM sub-partition, so it has to stay two instructions long.
+    uint32_t polls = 0;
+    long long t0 = 0;
 #endif
     while (!mbar_try_wait(bar, parity)) {
 #if B200_MBAR_TIMEOUT_CYCLES
-        if (clock64() - t0 > B200_MBAR_TIMEOUT_CYCLES) {
-            printf("b200attn: mbarrier wait timed out (block %d,%d thread %d bar@%u parity %u)\n",
-                   blockIdx.x, blockIdx.y, threadIdx.x, smem_u32(bar), parity);
-            __trap();
+        if ((++polls & 0xFFFu) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > B200_MBAR_TIMEOUT_CYCLES) {
+                printf("b200attn: mbarrier wait timed out (block %d,%d thread %d bar@%u parity %u)\n",
+                       blockIdx.x, blockIdx.y, threadIdx.x, smem_u32(bar), parity);
+                __trap();
+            }
         }
 #endif
     }

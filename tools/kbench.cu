@@ -106,7 +106,7 @@ int main(int argc, char** argv)
         for (int r = 0; r < 3; ++r)
             for (int j = 0; j < 8; ++j) {
                 printf("%-8s j=%2d:", names[r], 16 + j);
-                for (int e = 0; e < 6; ++e) printf(" %7lld", t[(r * 8 + j) * 8 + e] ? t[(r * 8 + j) * 8 + e] - t0 : -1);
+                for (int e = 0; e < 8; ++e) printf(" %7lld", t[(r * 8 + j) * 8 + e] ? t[(r * 8 + j) * 8 + e] - t0 : -1);
                 printf("\n");
             }
     }
