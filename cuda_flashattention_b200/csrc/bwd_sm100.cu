@@ -1,5 +1,5 @@
 // bwd_sm100.cu -- FlashAttention-2 backward for sm_100a (bf16, d = 128): dK/dV-stationary CTAs,
-// tcgen05 MMAs with every accumulator in TMEM, dQ reduced into an fp32 buffer by TMA reduce-add.
+// tcgen05 MMAs with every accumulator in TMEM, dQ reduced into an fp32 buffer by coalesced red.global.add.
 //
 // Replaces flash_attention_2_backward_kernel (reference
 // src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:47-246).  Same math --
@@ -17,7 +17,7 @@
 //   M3  dV  += P^T dO_i             TS   A = P^T from TMEM, B = dO_i as an MN-major operand
 //   M4  dK  += dS^T Q_i             TS   A = dS^T from TMEM, B = Q_i as an MN-major operand
 //   M5  dQ_i^T = K^T dS             SS   A = K (MN-major view), B = dS^T smem (MN-major) -> TMEM dQ
-//   drain warpgroup: dQ_i^T TMEM -> registers -> smem [64 q][128 d] fp32 -> cp.reduce.async.bulk (add)
+//   drain warpgroup: dQ_i^T TMEM -> registers -> coalesced fp32 red.global.add into the dQ accumulator
 // TMEM columns: S[0] 0..63, S[1] 64..127, dP 128..191, dQ^T 192..255, dV 256..383, dK 384..511.
 // Issue order per iteration i:  M1(i+1) | M3(i) M4(i) | M2(i+1) | M5(i)   (see DESIGN.md for the slack analysis)
 //
@@ -26,6 +26,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -34,12 +35,11 @@ constexpr int D = 128, BN = 128, BM = 64, NS = 3;
 constexpr int KV_BOX = BN * 128, KV_TILE = 2 * KV_BOX;        // 32 KB: [128 rows x 128 d] bf16 as 2 boxes of 64 d
 constexpr int Q_BOX = BM * 128, Q_TILE = 2 * Q_BOX;           // 16 KB: [64 rows x 128 d]
 constexpr int DS_TILE = BN * 128;                             // 16 KB: dS^T [128 kv rows x 64 q] bf16
-constexpr int DQ_STAGE = BM * D * 4;                          // 32 KB: [64 q][128 d] fp32
 constexpr int STAT_BYTES = BM * 4;                            // 256 B of L (or D) per Q tile
 constexpr int THREADS = 512;
 // smem carve-up (offsets from the 1024-aligned base)
 constexpr int OFF_K = 0, OFF_V = OFF_K + KV_TILE, OFF_Q = OFF_V + KV_TILE, OFF_DO = OFF_Q + NS * Q_TILE;
-constexpr int OFF_DS = OFF_DO + NS * Q_TILE, OFF_DQ = OFF_DS + 2 * DS_TILE, OFF_STAT = OFF_DQ + DQ_STAGE;
+constexpr int OFF_DS = OFF_DO + NS * Q_TILE, OFF_STAT = OFF_DS + 2 * DS_TILE;
 constexpr int OFF_BAR = OFF_STAT + NS * 2 * STAT_BYTES;
 constexpr int NBARS = 1 + 2 * NS + 2 + 1 + 2 + 1 + 2 + 1;
 constexpr int SMEM = 1024 + OFF_BAR + NBARS * 8 + 16;
@@ -47,12 +47,29 @@ static_assert(SMEM <= 227 * 1024, "backward shared memory budget");
 constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DQ = 192, TM_DV = 256, TM_DK = 384;
 }  // namespace bwd
 
+#ifdef B200_TRACE
+__device__ long long g_trace_bwd[3 * 8 * 8];
+#endif
+// roles: 0 = compute warpgroup 0 (its warp 0), 1 = dQ drain warpgroup (its warp 0), 2 = MMA issuer
+#define B200_TRB(role, i, ev) B200_TRACE_EVENT(g_trace_bwd, role, i, ev, (role) == 2 || (((threadIdx.x >> 5) & 3) == 0 && ((role) == 1 || threadIdx.x < 256)))
+
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+__device__ __forceinline__ void lds_f32x4(float* dst, uint32_t saddr) {
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(dst[0]), "=f"(dst[1]), "=f"(dst[2]), "=f"(dst[3]) : "r"(saddr));
+}
+__device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
+    asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(gaddr), "f"(v) : "memory");
+}
+
 // One compute warpgroup (w = 0/1 owns q columns 32w..32w+31 of every Q tile; thread = kv row).
+// The per-column statistics L_i, D_i are the same for every thread; they are fetched from shared
+// memory into registers BEFORE the wait for the MMA they go with, because shared memory is the
+// saturated resource of this kernel (the N = 64 SS MMAs alone ask for more than its 128 B/clk):
+// a load issued on the critical path queues behind operand traffic for hundreds of cycles.
 __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* smem, uint64_t* bar_in_full,
                                                  uint64_t* bar_S, uint64_t* bar_dP, uint64_t* bar_P, uint64_t* bar_dS,
                                                  int n_q, float scale_log2, float scale)
@@ -60,41 +77,53 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // kv row within the tile == TMEM lane
     const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    const uint32_t stat_base = smem_u32(smem + OFF_STAT) + 128 * w;    // + s * 2 * STAT_BYTES (+ STAT_BYTES for D)
     for (int i = 0; i < n_q; ++i) {
         const int b = i & 1, s = i % NS;
-        const float* Lq = reinterpret_cast<const float*>(smem + OFF_STAT + s * 2 * STAT_BYTES) + 32 * w;
-        const float* Dq = Lq + BM;
         const uint32_t tS = tmem + TM_S + 64 * b + 32 * w + lane_base;
         const uint32_t tP = tmem + TM_DP + 32 * w + lane_base;
         // ---- P^T = exp2(S^T * scale*log2e - L*log2e)
         mbar_wait(&bar_in_full[s], (i / NS) & 1);                       // L_i, D_i landed (same barrier as Q_i, dO_i)
+        float st[32];                                                   // L_i (log2 units), later D_i
+#pragma unroll
+        for (int c = 0; c < 8; ++c) lds_f32x4(st + 4 * c, stat_base + s * 2 * STAT_BYTES + 16 * c);
         mbar_wait(&bar_S[b], (i >> 1) & 1);
         tc_fence_after();
+        B200_TRB(0, i, 0);
         uint32_t sv[32];
         B200_TMEM_LD_32(tS, sv);
         tmem_wait_ld();
+        B200_TRB(0, i, 4);
         float p[32];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -Lq[c]));
+        for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
         {
             uint32_t pk[16];
 #pragma unroll
             for (int c = 0; c < 16; ++c) pk[c] = pack_bf16x2(p[2 * c], p[2 * c + 1]);
             B200_TMEM_ST_16(tS, pk);
         }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) lds_f32x4(st + 4 * c, stat_base + s * 2 * STAT_BYTES + STAT_BYTES + 16 * c);   // D_i, ahead of dP
+        B200_TRB(0, i, 5);
         tmem_wait_st();
+        B200_TRB(0, i, 6);
         tc_fence_before();
-        mbar_arrive(&bar_P[b]);
+        __syncwarp();
+        if (lane0) mbar_arrive(&bar_P[b]);
+        B200_TRB(0, i, 1);
         // ---- dS^T = scale * P^T o (dP^T - D)
         mbar_wait(bar_dP, i & 1);
         tc_fence_after();
+        B200_TRB(0, i, 2);
         B200_TMEM_LD_32(tP, sv);
         tmem_wait_ld();
         uint32_t dk[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
-            const float a0 = p[2 * c] * (__uint_as_float(sv[2 * c]) - Dq[2 * c]) * scale;
-            const float a1 = p[2 * c + 1] * (__uint_as_float(sv[2 * c + 1]) - Dq[2 * c + 1]) * scale;
+            const float a0 = p[2 * c] * (__uint_as_float(sv[2 * c]) - st[2 * c]) * scale;
+            const float a1 = p[2 * c + 1] * (__uint_as_float(sv[2 * c + 1]) - st[2 * c + 1]) * scale;
             dk[c] = pack_bf16x2(a0, a1);
         }
         B200_TMEM_ST_16(tP, dk);
@@ -106,36 +135,49 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         fence_proxy_async_smem();
         tmem_wait_st();
         tc_fence_before();
-        mbar_arrive(bar_dS);
+        __syncwarp();
+        if (lane0) mbar_arrive(bar_dS);
+        B200_TRB(0, i, 3);
     }
 }
 
-// dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> smem [64 q][128 d] fp32 -> TMA reduce-add.
-__device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint8_t* smem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
-                                               const CUtensorMap* tmdQ, int n_q, int bh)
+// dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> registers -> fp32 red.global.add straight
+// into the dQ accumulator.  A warp's 32 lanes hold 32 consecutive d of one q row, so every red
+// instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
+__device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
+                                               float* __restrict__ dQacc, int Nq, int n_q, int i_off, int bh, int dbg)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
     const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
-    float* stage = reinterpret_cast<float*>(smem + OFF_DQ);
+    const bool lane0 = (threadIdx.x & 31) == 0;
     for (int i = 0; i < n_q; ++i) {
+        int qt = i + i_off;                                            // the q tile this iteration works on
+        if (qt >= n_q) qt -= n_q;
         mbar_wait(bar_dQ_full, i & 1);
         tc_fence_after();
+        B200_TRB(1, i, 0);
         uint32_t v[64];
         B200_TMEM_LD_32(tQ, v);
         B200_TMEM_LD_32(tQ + 32, v + 32);
         tmem_wait_ld();
         tc_fence_before();
-        mbar_arrive(bar_dQ_empty);                                     // TMEM columns are free again
-        if (r == 0) tma_store_wait_read<0>();                          // previous reduce has finished reading the stage
-        named_bar_sync(3, 128);
+        __syncwarp();
+        if (lane0) mbar_arrive(bar_dQ_empty);                          // TMEM columns are free again
+        B200_TRB(1, i, 1);
+        float* dst = dQacc + ((size_t)bh * Nq + (size_t)qt * BM) * D + r;
+        const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
+        if (!(dbg & 1)) {
+            if (q_valid == BM) {
 #pragma unroll
-        for (int q = 0; q < 64; ++q) stage[q * D + r] = __uint_as_float(v[q]);   // a warp writes 32 consecutive floats
-        fence_proxy_async_smem();
-        named_bar_sync(3, 128);
-        if (r == 0) { tma_reduce_add_3d(tmdQ, stage, 0, i * BM, bh); tma_store_commit(); }
+                for (int q = 0; q < BM; ++q) red_add_f32(dst + q * D, __uint_as_float(v[q]));
+            } else {
+#pragma unroll
+                for (int q = 0; q < BM; ++q) if (q < q_valid) red_add_f32(dst + q * D, __uint_as_float(v[q]));
+            }
+        }
+        B200_TRB(1, i, 2);
     }
-    if (r == 0) tma_store_wait<0>();
 }
 
 // dV (w = 0) / dK (w = 1) epilogue: TMEM fp32 [128 kv x 128 d] -> bf16 -> swizzled smem -> TMA store.
@@ -174,9 +216,9 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 __global__ void __launch_bounds__(bwd::THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
-           const __grid_constant__ CUtensorMap tmdQ, const __grid_constant__ CUtensorMap tmdK,
+           float* __restrict__ dQacc, const __grid_constant__ CUtensorMap tmdK,
            const __grid_constant__ CUtensorMap tmdV, const float* __restrict__ L2p, const float* __restrict__ Dp,
-           int Nq, int Nq_pad, float scale_log2, float scale)
+           int Nq, int Nq_pad, float scale_log2, float scale, int dbg)
 {
     using namespace bwd;
     extern __shared__ uint8_t smem_raw[];
@@ -187,26 +229,30 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint64_t* bar_in_empty = bar_in_full + NS;   // [NS]
     uint64_t* bar_S = bar_in_empty + NS;         // [2]   S^T(i) complete
     uint64_t* bar_dP = bar_S + 2;                // [1]   dP^T(i) complete
-    uint64_t* bar_P = bar_dP + 1;                // [2]   P^T(i) written (256 arrivals)
-    uint64_t* bar_dS = bar_P + 2;                // [1]   dS^T(i) written to TMEM + smem (256 arrivals)
+    uint64_t* bar_P = bar_dP + 1;                // [2]   P^T(i) written (one arrival per compute warp)
+    uint64_t* bar_dS = bar_P + 2;                // [1]   dS^T(i) written to TMEM + smem (one arrival per compute warp)
     uint64_t* bar_dQ_full = bar_dS + 1;          // [1]
-    uint64_t* bar_dQ_empty = bar_dQ_full + 1;    // [1]   (128 arrivals)
+    uint64_t* bar_dQ_empty = bar_dQ_full + 1;    // [1]   (one arrival per drain warp)
     uint64_t* bar_done = bar_dQ_empty + 1;       // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
 
     const int warp = threadIdx.x >> 5;
     const int bh = blockIdx.y, kv0 = blockIdx.x * BN;
     const int n_q = (Nq + BM - 1) / BM;
+    // Every CTA of a (b,h) slab walks the q tiles in the same cyclic order but starts at a different
+    // one: at any moment the CTAs that run together reduce-add into DIFFERENT dQ tiles, so their
+    // fp32 atomics do not queue up on the same L2 lines.
+    const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x);
 
     if (threadIdx.x == 0) {
         mbar_init(bar_KV, 1);
         for (int s = 0; s < NS; ++s) { mbar_init(&bar_in_full[s], 1); mbar_init(&bar_in_empty[s], 1); }
         mbar_init(&bar_S[0], 1); mbar_init(&bar_S[1], 1); mbar_init(bar_dP, 1);
-        mbar_init(&bar_P[0], 256); mbar_init(&bar_P[1], 256); mbar_init(bar_dS, 256);
-        mbar_init(bar_dQ_full, 1); mbar_init(bar_dQ_empty, 128); mbar_init(bar_done, 1);
+        mbar_init(&bar_P[0], 8); mbar_init(&bar_P[1], 8); mbar_init(bar_dS, 8);
+        mbar_init(bar_dQ_full, 1); mbar_init(bar_dQ_empty, 4); mbar_init(bar_done, 1);
         fence_mbar_init();
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmdO);
-        tma_prefetch_desc(&tmdQ); tma_prefetch_desc(&tmdK); tma_prefetch_desc(&tmdV);
+        tma_prefetch_desc(&tmdK); tma_prefetch_desc(&tmdV);
     }
     if (warp == 2) { tmem_alloc<512>(tmem_slot); tmem_relinquish(); }
     tc_fence_before();
@@ -226,14 +272,16 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             const float* Drow = Dp + (size_t)bh * Nq_pad;
             for (int i = 0; i < n_q; ++i) {
                 const int s = i % NS;
+                int qt = i + i_off;
+                if (qt >= n_q) qt -= n_q;
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
                 mbar_expect_tx(&bar_in_full[s], 2 * Q_TILE + 2 * STAT_BYTES);
                 for (int b = 0; b < 2; ++b) {
-                    tma_load_3d(smem + OFF_Q + s * Q_TILE + b * Q_BOX, &tmQ, &bar_in_full[s], b * 64, i * BM, bh, kEvictLast);
-                    tma_load_3d(smem + OFF_DO + s * Q_TILE + b * Q_BOX, &tmdO, &bar_in_full[s], b * 64, i * BM, bh, kEvictLast);
+                    tma_load_3d(smem + OFF_Q + s * Q_TILE + b * Q_BOX, &tmQ, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
+                    tma_load_3d(smem + OFF_DO + s * Q_TILE + b * Q_BOX, &tmdO, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
                 }
-                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES, Lrow + i * BM, STAT_BYTES, &bar_in_full[s]);
-                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES + STAT_BYTES, Drow + i * BM, STAT_BYTES, &bar_in_full[s]);
+                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES, Lrow + qt * BM, STAT_BYTES, &bar_in_full[s]);
+                bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES + STAT_BYTES, Drow + qt * BM, STAT_BYTES, &bar_in_full[s]);
             }
         }
     } else if (warp == 1) {
@@ -271,16 +319,22 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                     tc_fence_after();
                     M1(i + 1);
                 }
+                B200_TRB(2, i, 0);
                 mbar_wait(&bar_P[b], (i >> 1) & 1);
                 tc_fence_after();
+                B200_TRB(2, i, 1);
                 mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, i > 0);          // M3: dV += P^T dO_i
+                B200_TRB(2, i, 2);
                 mbar_wait(bar_dS, i & 1);
                 tc_fence_after();
+                B200_TRB(2, i, 3);
                 mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
                 umma_commit(&bar_in_empty[s]);
                 if (i + 1 < n_q) M2(i + 1);
+                B200_TRB(2, i, 4);
                 mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
                 tc_fence_after();
+                B200_TRB(2, i, 5);
                 {                                                                       // M5: dQ_i^T = K^T dS
                     const uint64_t ad = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
                     const uint64_t bd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
@@ -289,6 +343,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                         umma_f16_ss(tmem + TM_DQ, sdesc_advance(ad, kk * 2048), sdesc_advance(bd, kk * 2048), idesc_dq, kk > 0);
                 }
                 umma_commit(bar_dQ_full);
+                B200_TRB(2, i, 6);
             }
             umma_commit(bar_done);
         }
@@ -299,7 +354,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         tc_fence_after();
         bwd_epilogue(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
     } else if (warp >= 12) {
-        bwd_drain_role(tmem, smem, bar_dQ_full, bar_dQ_empty, &tmdQ, n_q, bh);
+        bwd_drain_role(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_q, i_off, bh, dbg);
     }
 
     tc_fence_before();
@@ -335,6 +390,15 @@ cast_dq_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, s
         reinterpret_cast<uint2*>(out)[i] = o;
     }
 }
+
+#ifdef B200_TRACE
+int bwd_trace_read(long long* out, int n)
+{
+    if (n > 3 * 8 * 8) n = 3 * 8 * 8;
+    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_trace_bwd, n * sizeof(long long)));
+    return n;
+}
+#endif
 
 static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -377,16 +441,17 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
     count_launch();
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
 
-    CUtensorMap tmQ, tmK, tmV, tmdO, tmdQ, tmdK, tmdV;
+    CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
     const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, D, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, D, BM, 64) ||
         make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, D, BN, 64) ||
-        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64) ||
-        make_tmap_3d(&tmdQ, dQacc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, BH, Nq, D, BM, D, CU_TENSOR_MAP_SWIZZLE_NONE))
+        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64))
         return B200_ERR_CUDA;
     dim3 grid((Nkv + BN - 1) / BN, BH);
-    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, tmdQ, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
-                                            scale * 1.4426950408889634f, scale);
+    static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
+    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? atoi(e) : 0; }
+    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
+                                            scale * 1.4426950408889634f, scale, dbg);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);

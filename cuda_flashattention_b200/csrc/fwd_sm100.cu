@@ -25,17 +25,10 @@
 
 namespace b200 {
 
-// Optional in-kernel event trace (build with EXTRA=-DB200_TRACE): CTA (0,0) records clock64() at the
-// hand-off points of iterations 16..23; read back with b200_debug_trace_read.  Compiled out otherwise.
 #ifdef B200_TRACE
 __device__ long long g_trace[3 * 8 * 8];
-#define B200_TR(role, j, ev)                                                                       \
-    do { if (blockIdx.x == 0 && blockIdx.y == 0 && (j) >= 16 && (j) < 24 && (threadIdx.x & 31) == 0 && \
-             ((role) == 2 || ((threadIdx.x >> 5) & 3) == 0))                                        \
-            g_trace[((role) * 8 + ((j) - 16)) * 8 + (ev)] = clock64(); } while (0)
-#else
-#define B200_TR(role, j, ev) do {} while (0)
 #endif
+#define B200_TR(role, j, ev) B200_TRACE_EVENT(g_trace, role, j, ev, (role) == 2 || ((threadIdx.x >> 5) & 3) == 0)
 
 // POLY = how many of every 16 (score, score) pairs get their exp2 from the FMA-pipe polynomial
 // instead of the MUFU (bf16 only); SPLITP = P is published to the MMA warp in two halves.

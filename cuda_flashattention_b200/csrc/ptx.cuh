@@ -312,4 +312,17 @@ __device__ __forceinline__ void exp2_poly2(uint64_t x, float& p_lo, float& p_hi)
     p_hi = __uint_as_float((__float_as_uint(th) << 23) + __float_as_uint(ph));
 }
 
+// ------------------------------------------------------------------ optional in-kernel event trace
+// Build with EXTRA=-DB200_TRACE (make TRACE=1): CTA (0,0) records clock64() into arr[role][j-16][ev]
+// for loop iterations 16..23 at the hand-off points of a kernel; `who` selects the recording warp
+// (lane 0 of it writes).  Read back with b200_debug_trace_read; tools/kbench --trace prints it.
+// Compiled out otherwise.
+#ifdef B200_TRACE
+#define B200_TRACE_EVENT(arr, role, j, ev, who)                                                         \
+    do { if (blockIdx.x == 0 && blockIdx.y == 0 && (j) >= 16 && (j) < 24 && (threadIdx.x & 31) == 0 && (who)) \
+            arr[((role) * 8 + ((j) - 16)) * 8 + (ev)] = clock64(); } while (0)
+#else
+#define B200_TRACE_EVENT(arr, role, j, ev, who) do {} while (0)
+#endif
+
 }  // namespace b200

@@ -53,7 +53,7 @@ int main(int argc, char** argv)
     fwd_t fwd = (fwd_t)dlsym(h, "b200_fa2_fwd");
     bwd_t bwd = (bwd_t)dlsym(h, "b200_fa2_bwd");
     ws_t wsb = (ws_t)dlsym(h, "b200_fa2_bwd_workspace_bytes");
-    trace_t tr = (trace_t)dlsym(h, "b200_debug_trace_read");
+    trace_t tr = (trace_t)dlsym(h, strcmp(mode, "bwd") == 0 ? "b200_debug_trace_read_bwd" : "b200_debug_trace_read");
     if (!fwd || !bwd || !wsb) { fprintf(stderr, "missing symbols\n"); return 2; }
 
     const size_t n = (size_t)B * H * N * d, eb = f32 ? 4 : 2;
@@ -102,7 +102,8 @@ int main(int argc, char** argv)
         long long t[3 * 8 * 8];
         tr(t, 3 * 8 * 8);
         const long long t0 = t[0];
-        const char* names[3] = {"softmax0", "softmax1", "mma"};
+        const char* names_f[3] = {"softmax0", "softmax1", "mma"}, *names_b[3] = {"compute0", "drain", "mma"};
+        const char** names = strcmp(mode, "bwd") == 0 ? names_b : names_f;
         for (int r = 0; r < 3; ++r)
             for (int j = 0; j < 8; ++j) {
                 printf("%-8s j=%2d:", names[r], 16 + j);
