@@ -414,6 +414,32 @@ size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
     return 2 * al256((size_t)BH * Nq_pad * sizeof(float)) + al256((size_t)BH * Nq * d * sizeof(float));
 }
 
+static int bwd_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
+                      float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st)
+{
+    using namespace bwd;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        attr_set = true;
+    }
+    const int Nq_pad = (Nq + 63) / 64 * 64;
+    CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
+    const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, D, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, D, BM, 64) ||
+        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, D, BN, 64) ||
+        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64))
+        return B200_ERR_CUDA;
+    dim3 grid((Nkv + BN - 1) / BN, BH);
+    static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
+    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
+    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
+                                            scale * 1.4426950408889634f, scale, dbg);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* Dvec,
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
            void* ws, size_t ws_bytes, cudaStream_t st)
@@ -423,11 +449,6 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
     if ((align & 15) != 0 || BH > 65535)
         return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
     if (ws_bytes < tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype)) return B200_ERR_WORKSPACE;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        attr_set = true;
-    }
     const int Nq_pad = (Nq + 63) / 64 * 64;
     uint8_t* p = reinterpret_cast<uint8_t*>(ws);
     float* L2p = reinterpret_cast<float*>(p); p += al256((size_t)BH * Nq_pad * sizeof(float));
@@ -440,26 +461,46 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
-
-    CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
-    const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, D, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, D, BM, 64) ||
-        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, D, BN, 64) ||
-        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64))
-        return B200_ERR_CUDA;
-    dim3 grid((Nkv + BN - 1) / BN, BH);
-    static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
-    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? atoi(e) : 0; }
-    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
-                                            scale * 1.4426950408889634f, scale, dbg);
-    B200_CUDA_TRY(cudaGetLastError());
-    count_launch();
+    B200_TRY(bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st));
     unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
     if (cgrid > 148u * 8) cgrid = 148u * 8;
     cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
+}
+
+// ---- pieces for the ring backward: statistics once per call; per ring step one launch that adds
+//      its dQ into the caller's fp32 accumulator (no zeroing, no cast) and writes bf16 dK/dV partials
+bool tc_bwd_ring_supported(int dtype, int d, int BH, const void* Q, const void* K, const void* V, const void* dO)
+{
+    const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO;
+    return dtype == B200_DTYPE_BF16 && d == 128 && (align & 15) == 0 && BH <= 65535;
+}
+size_t tc_bwd_ring_stats_bytes(int BH, int Nq)
+{
+    const size_t Nq_pad = (size_t)(Nq + 63) / 64 * 64;
+    return 2 * al256((size_t)BH * Nq_pad * sizeof(float));
+}
+int tc_bwd_ring_prepare(const float* L, const float* Dvec, void* stats, int BH, int Nq, cudaStream_t st)
+{
+    const int Nq_pad = (Nq + 63) / 64 * 64;
+    float* L2p = reinterpret_cast<float*>(stats);
+    float* Dp = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
+    const size_t total = (size_t)BH * Nq_pad;
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+// dQacc (fp32 [BH, Nq, 128]) += dQ(block);  dKp / dVp (bf16 [BH, Nkv, 128]) = dK(block), dV(block)
+int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
+                     float* dQacc, void* dKp, void* dVp, int BH, int Nq, int Nkv, float scale, cudaStream_t st)
+{
+    const int Nq_pad = (Nq + 63) / 64 * 64;
+    const float* L2p = reinterpret_cast<const float*>(stats);
+    const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
+    return bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, scale, st);
 }
 
 }  // namespace b200

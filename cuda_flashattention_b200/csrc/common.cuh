@@ -47,6 +47,13 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
            void* ws, size_t ws_bytes, cudaStream_t st);
 
+// ring backward building blocks (bf16, d = 128): padded statistics once, then accumulate-only steps
+bool tc_bwd_ring_supported(int dtype, int d, int BH, const void* Q, const void* K, const void* V, const void* dO);
+size_t tc_bwd_ring_stats_bytes(int BH, int Nq);
+int tc_bwd_ring_prepare(const float* L, const float* D, void* stats, int BH, int Nq, cudaStream_t st);
+int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
+                     float* dQacc, void* dKp, void* dVp, int BH, int Nq, int Nkv, float scale, cudaStream_t st);
+
 // ---- per-device scratch arena (api.cu) ------------------------------------------------------------
 // Grows monotonically; reuse across calls is safe because all users are stream-ordered on the
 // caller's stream and growth synchronises the device before freeing the old block.

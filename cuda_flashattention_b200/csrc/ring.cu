@@ -12,7 +12,11 @@
 //   * a ring BACKWARD exists (the reference has none): (K, V, dK, dV) rotate, Q/dO/O/L/dQ stay.
 #include "common.cuh"
 #include <nccl.h>
+#include <cuda.h>
 #include <mutex>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
 
 namespace b200 {
 
@@ -64,6 +68,165 @@ static int ring_scratch(RingState* s, size_t bytes, void** out)
     return B200_OK;
 }
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// ---------------------------------------------------------------------------------------------
+// Copy-engine transport.  NCCL's send/recv kernels occupy SMs for the whole transfer, and an SM
+// that hosts an NCCL CTA cannot host an attention CTA (ours take the whole register file), which
+// costs ~20 % of a ring step.  So the K/V (and dK/dV accumulator) blocks are PUSHED into the next
+// rank's receive buffer with cudaMemcpyAsync over NVLink -- DMA engines, zero SMs -- through a
+// CUDA-IPC mapping of the peer's scratch, and ordered with stream memory operations on small
+// counters (cuStreamWriteValue32 into the peer's flags, cuStreamWaitValue32 on our own).  NCCL is
+// still the bootstrap (all-gather of the IPC handles on the caller's communicator) and the
+// fallback when IPC / peer access is unavailable or B200_RING_TRANSPORT=nccl.
+// Every rank runs the same call sequence, so "how many times has my neighbour filled / released
+// buffer x" is known locally: the counters only ever grow and are never reset between calls.
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_memop32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static PFN_memop32 g_wait32 = nullptr, g_write32 = nullptr;
+static bool load_memops()
+{
+    if (g_wait32 && g_write32) return true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return false;
+    g_wait32 = reinterpret_cast<PFN_memop32>(p);
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return false;
+    g_write32 = reinterpret_cast<PFN_memop32>(p);
+    return true;
+}
+
+enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_COUNT = 16 };
+
+struct PeerLink {
+    ncclComm_t comm = nullptr;
+    int rank = -1, nranks = 0;
+    bool ok = false;                        // copy-engine transport usable with `comm`
+    uint32_t* flags = nullptr;              // my counters (written by my neighbours)
+    uint8_t* xchg = nullptr;                // device staging for the handle all-gather
+    uint8_t* next_buf = nullptr;            // IPC mapping of the next rank's scratch
+    uint32_t* next_flags = nullptr;
+    uint32_t* prev_flags = nullptr;
+    void* opened[4] = {nullptr, nullptr, nullptr, nullptr};   // mappings to close
+    size_t exported = 0;                    // scratch size the neighbours have mapped
+    uint32_t push_kv[2] = {0, 0}, in_kv[2] = {0, 0}, rel_kv[2] = {0, 0};
+    uint32_t push_acc[2] = {0, 0}, in_acc[2] = {0, 0}, out_acc[2] = {0, 0};
+};
+static PeerLink g_link[64];
+
+struct LinkMsg {                            // what every rank publishes
+    cudaIpcMemHandle_t buf, flags;
+    unsigned long long bytes;
+    int ok;
+    int pad;
+};
+
+static void link_close(PeerLink& L)
+{
+    for (int i = 0; i < 4; ++i)
+        if (L.opened[i]) { cudaIpcCloseMemHandle(L.opened[i]); L.opened[i] = nullptr; }
+    L.next_buf = nullptr; L.next_flags = nullptr; L.prev_flags = nullptr;
+    (void)cudaGetLastError();
+}
+
+static int link_allgather(PeerLink& L, RingState* rs, const LinkMsg& mine, LinkMsg* all)
+{
+    const size_t sz = sizeof(LinkMsg);
+    B200_CUDA_TRY(cudaMemcpyAsync(L.xchg, &mine, sz, cudaMemcpyHostToDevice, rs->comm_stream));
+    B200_NCCL_TRY(ncclAllGather(L.xchg, L.xchg + 256, sz, ncclInt8, L.comm, rs->comm_stream));
+    B200_CUDA_TRY(cudaMemcpyAsync(all, L.xchg + 256, sz * L.nranks, cudaMemcpyDeviceToHost, rs->comm_stream));
+    B200_CUDA_TRY(cudaStreamSynchronize(rs->comm_stream));
+    return B200_OK;
+}
+
+// Makes sure the scratch is at least `need` bytes and that the copy-engine link (if usable at
+// all) points at the neighbours' current scratch.  Collective: every rank of `comm` gets here in
+// the same call with the same `need`.  Returns L.ok through *use_ce.
+static int link_prepare(RingState* rs, ncclComm_t comm, int rank, int nranks, size_t need, void** scratch, bool* use_ce)
+{
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    PeerLink& L = g_link[dev];
+    static int want_ce = -1;
+    if (want_ce < 0) { const char* e = getenv("B200_RING_TRANSPORT"); want_ce = (e && !strcmp(e, "nccl")) ? 0 : 1; }
+    const bool new_comm = (L.comm != comm || L.rank != rank || L.nranks != nranks);
+    const bool grow = rs->bytes < need;
+    if (!want_ce || nranks > 255) {
+        B200_TRY(ring_scratch(rs, need, scratch));
+        *use_ce = false;
+        return B200_OK;
+    }
+    if (!new_comm && !grow) { *scratch = rs->buf; *use_ce = L.ok; return B200_OK; }
+
+    // ---- (re)build the link: quiesce, drop the old mappings, agree, re-map
+    B200_CUDA_TRY(cudaDeviceSynchronize());
+    link_close(L);
+    if (new_comm) {
+        uint32_t* keep_flags = L.flags; uint8_t* keep_xchg = L.xchg;
+        L = PeerLink();
+        L.flags = keep_flags; L.xchg = keep_xchg;
+        L.comm = comm; L.rank = rank; L.nranks = nranks;
+    }
+    if (!L.flags) {
+        B200_CUDA_TRY(cudaMalloc(&L.flags, F_COUNT * sizeof(uint32_t)));
+        B200_CUDA_TRY(cudaMalloc(&L.xchg, 256 + 256 * 256));
+    }
+    if (new_comm) B200_CUDA_TRY(cudaMemset(L.flags, 0, F_COUNT * sizeof(uint32_t)));
+    LinkMsg mine, all[256];
+    memset(&mine, 0, sizeof(mine));
+    static_assert(sizeof(LinkMsg) <= 256, "LinkMsg must fit its all-gather slot");
+    // round 1 doubles as a barrier: after it nobody maps my old scratch any more and every rank has zeroed its flags
+    B200_TRY(link_allgather(L, rs, mine, all));
+    B200_TRY(ring_scratch(rs, need, scratch));
+    bool ok = load_memops();
+    if (ok) ok = cudaIpcGetMemHandle(&mine.buf, rs->buf) == cudaSuccess && cudaIpcGetMemHandle(&mine.flags, L.flags) == cudaSuccess;
+    mine.bytes = rs->bytes; mine.ok = ok ? 1 : 0;
+    (void)cudaGetLastError();
+    B200_TRY(link_allgather(L, rs, mine, all));
+    const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
+    for (int r = 0; r < nranks; ++r) ok = ok && all[r].ok && all[r].bytes == rs->bytes;
+    if (ok) {
+        void* nb = nullptr; void* nf = nullptr; void* pf = nullptr;
+        ok = cudaIpcOpenMemHandle(&nb, all[next].buf, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess &&
+             cudaIpcOpenMemHandle(&nf, all[next].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+        L.opened[0] = nb; L.opened[1] = nf;
+        if (ok) {
+            if (prev == next) pf = nf;
+            else { ok = cudaIpcOpenMemHandle(&pf, all[prev].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess; L.opened[2] = pf; }
+        }
+        L.next_buf = reinterpret_cast<uint8_t*>(nb); L.next_flags = reinterpret_cast<uint32_t*>(nf); L.prev_flags = reinterpret_cast<uint32_t*>(pf);
+        (void)cudaGetLastError();
+    }
+    // round 3: the link is used only if EVERY rank managed to map its neighbours
+    memset(&mine, 0, sizeof(mine));
+    mine.ok = ok ? 1 : 0;
+    B200_TRY(link_allgather(L, rs, mine, all));
+    for (int r = 0; r < nranks; ++r) ok = ok && all[r].ok;
+    if (!ok) link_close(L);
+    L.ok = ok; L.exported = rs->bytes;
+    *use_ce = ok;
+    return B200_OK;
+}
+
+#define B200_CU_TRY(call) do { if ((call) != CUDA_SUCCESS) return B200_ERR_CUDA; } while (0)
+static inline int wait_ge(cudaStream_t st, uint32_t* addr, uint32_t v)
+{
+    B200_CU_TRY(g_wait32(st, (CUdeviceptr)(uintptr_t)addr, v, CU_STREAM_WAIT_VALUE_GEQ));
+    return B200_OK;
+}
+static inline int write_val(cudaStream_t st, uint32_t* addr, uint32_t v)
+{
+    B200_CU_TRY(g_write32(st, (CUdeviceptr)(uintptr_t)addr, v, CU_STREAM_WRITE_VALUE_DEFAULT));
+    return B200_OK;
+}
+// push two buffers into the next rank's K/V receive slot
+static int ce_push_kv(PeerLink& L, RingState* rs, int slot, const void* k, const void* v, size_t off_k, size_t off_v, size_t bytes)
+{
+    const uint32_t n = ++L.push_kv[slot];
+    if (n > 1) B200_TRY(wait_ge(rs->comm_stream, L.flags + F_FREE_KV + slot, n - 1));   // neighbour done with the previous fill
+    B200_CUDA_TRY(cudaMemcpyAsync(L.next_buf + off_k, k, bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
+    B200_CUDA_TRY(cudaMemcpyAsync(L.next_buf + off_v, v, bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
+    return write_val(rs->comm_stream, L.next_flags + F_RDY_KV + slot, n);
+}
 
 // acc[i] += (float)part[i]
 template <typename T>
@@ -121,6 +284,9 @@ static int cast_out(void* out, const float* acc, size_t n, int dtype, cudaStream
 static int exchange(const void* const* send, void* const* recv, const size_t* bytes, int n, int next, int prev,
                     ncclComm_t comm, cudaStream_t st)
 {
+    static int dbg = -1;                 // experiment hook: B200_RING_DBG=1 skips the transfers (timing only, wrong results)
+    if (dbg < 0) { const char* e = getenv("B200_RING_DBG"); dbg = e ? atoi(e) : 0; }
+    if (dbg & 1) return B200_OK;
     B200_NCCL_TRY(ncclGroupStart());
     for (int i = 0; i < n; ++i) {
         B200_NCCL_TRY(ncclSend(send[i], bytes[i], ncclInt8, next, comm, st));
@@ -165,6 +331,8 @@ int b200_ring_comm_init(ncclComm_t* comm, const void* id128, int rank, int nrank
 int b200_ring_comm_destroy(ncclComm_t comm)
 {
     if (!comm) return B200_OK;
+    for (int i = 0; i < 64; ++i)
+        if (g_link[i].comm == comm) { link_close(g_link[i]); g_link[i].comm = nullptr; g_link[i].ok = false; }
     B200_NCCL_TRY(ncclCommDestroy(comm));
     return B200_OK;
 }
@@ -198,11 +366,17 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
     // scratch: 2 x (K,V) receive buffers + partial O + partial LSE
     const size_t total = 4 * align256(kv_bytes) + align256(kv_bytes) + align256(l_bytes);
     void* base;
-    B200_TRY(ring_scratch(rs, total, &base));
+    bool ce = false;
+    B200_TRY(link_prepare(rs, comm, rank, nranks, total, &base, &ce));
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    PeerLink& lk = g_link[dev];
     uint8_t* p = reinterpret_cast<uint8_t*>(base);
-    void* Kb[2]; void* Vb[2];
-    Kb[0] = p; p += align256(kv_bytes); Vb[0] = p; p += align256(kv_bytes);
-    Kb[1] = p; p += align256(kv_bytes); Vb[1] = p; p += align256(kv_bytes);
+    void* Kb[2]; void* Vb[2]; size_t offK[2], offV[2];
+    for (int i = 0; i < 2; ++i) {
+        offK[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Kb[i] = p; p += align256(kv_bytes);
+        offV[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Vb[i] = p; p += align256(kv_bytes);
+    }
     void* Op = p; p += align256(kv_bytes);
     float* Lp = reinterpret_cast<float*>(p);
 
@@ -214,14 +388,25 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
     const void* Kc = K; const void* Vc = V;
     for (int step = 0; step < nranks; ++step) {
         const int slot = step & 1;            // receive slot for the block used at step+1
+        const int cur_slot = slot ^ 1;        // slot holding the block of this step (step >= 1)
+        if (ce && step >= 1) {
+            // the block of this step was pushed into cur_slot by the previous rank: both streams wait for it
+            const uint32_t k = ++lk.in_kv[cur_slot];
+            B200_TRY(wait_ge(st, lk.flags + F_RDY_KV + cur_slot, k));
+            B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_RDY_KV + cur_slot, k));
+        }
         if (step < nranks - 1) {
-            // receive slot `slot` held the block that step-1 attended to; wait until that read is done
-            if (step >= 2) B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[slot], 0));
-            const void* s[2] = {Kc, Vc};
-            void* r[2] = {Kb[slot], Vb[slot]};
-            size_t b[2] = {kv_bytes, kv_bytes};
-            B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
-            B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[slot], rs->comm_stream));
+            if (ce) {
+                B200_TRY(ce_push_kv(lk, rs, slot, Kc, Vc, offK[slot], offV[slot], kv_bytes));
+            } else {
+                // receive slot `slot` held the block that step-1 attended to; wait until that read is done
+                if (step >= 2) B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[slot], 0));
+                const void* s[2] = {Kc, Vc};
+                void* r[2] = {Kb[slot], Vb[slot]};
+                size_t b[2] = {kv_bytes, kv_bytes};
+                B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[slot], rs->comm_stream));
+            }
         }
         // attention of the local queries against the current block (overlaps the exchange above)
         if (step == 0) {
@@ -230,12 +415,24 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
             B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, st));
             B200_TRY(b200_lse_merge(O, L, Op, Lp, B, H, Nl, d, dtype, st));
         }
-        if (step < nranks - 1) {
+        if (ce) {
+            if (step >= 1) {
+                // cur_slot is free again once this step's attention AND its onward push are done: tell the sender
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_compute[cur_slot], st));
+                B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[cur_slot], 0));
+                B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
+            }
+        } else if (step < nranks - 1) {
             // block of step (in slot^1 for step >= 1) is now free for the receive of step+1
             B200_CUDA_TRY(cudaEventRecord(rs->ev_compute[slot ^ 1], st));
             B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[slot], 0));
-            Kc = Kb[slot]; Vc = Vb[slot];
         }
+        if (step < nranks - 1) { Kc = Kb[slot]; Vc = Vb[slot]; }
+    }
+    if (ce) {
+        // the caller may reuse K/V (the source of the first push) once its stream has passed this call
+        B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
+        B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
     }
     return B200_OK;
 }
@@ -257,11 +454,22 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t n_el = (size_t)B * H * Nl * d;
     const size_t kv_bytes = n_el * es, acc_bytes = n_el * sizeof(float);
-    // scratch: 2 x (K,V) recv, 3 partial grads (I/O dtype), dQ fp32 acc, 2 x (dK,dV) fp32 acc
-    const size_t total = 4 * align256(kv_bytes) + 3 * align256(kv_bytes) + align256(acc_bytes) + 4 * align256(acc_bytes);
+    // tensor-core steps (bf16, d = 128): D and the padded statistics are computed once per call and each step adds
+    // its dQ straight into the fp32 accumulator; otherwise every step is a full b200_fa2_bwd + accumulate
+    const bool fused = tc_bwd_ring_supported(dtype, d, B * H, Q, K, V, dO) && b200_bwd_uses_tensor_cores(dtype, d, Nl, Nl);
+    const size_t d_bytes = align256((size_t)B * H * Nl * sizeof(float));
+    const size_t stats_bytes = fused ? tc_bwd_ring_stats_bytes(B * H, Nl) : 0;
+    // scratch: 2 x (K,V) recv, 3 partial grads (I/O dtype), dQ fp32 acc, 2 x (dK,dV) fp32 acc, D, padded stats
+    const size_t total = 4 * align256(kv_bytes) + 3 * align256(kv_bytes) + align256(acc_bytes) + 4 * align256(acc_bytes) +
+                         d_bytes + align256(stats_bytes);
     void* base;
-    B200_TRY(ring_scratch(rs, total, &base));
+    bool ce = false;
+    B200_TRY(link_prepare(rs, comm, rank, nranks, total, &base, &ce));
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    PeerLink& lk = g_link[dev];
     uint8_t* p = reinterpret_cast<uint8_t*>(base);
+    auto off = [&](const void* q) { return (size_t)(reinterpret_cast<const uint8_t*>(q) - reinterpret_cast<uint8_t*>(base)); };
     void* Kb[2]; void* Vb[2]; float* dKa[2]; float* dVa[2];
     Kb[0] = p; p += align256(kv_bytes); Vb[0] = p; p += align256(kv_bytes);
     Kb[1] = p; p += align256(kv_bytes); Vb[1] = p; p += align256(kv_bytes);
@@ -273,8 +481,14 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
         dKa[i] = reinterpret_cast<float*>(p); p += align256(acc_bytes);
         dVa[i] = reinterpret_cast<float*>(p); p += align256(acc_bytes);
     }
+    float* Dvec = reinterpret_cast<float*>(p); p += d_bytes;
+    void* stats = p;
     const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
 
+    if (fused) {
+        B200_TRY(rowdot(dO, O, Dvec, (size_t)B * H * Nl, d, dtype, st));
+        B200_TRY(tc_bwd_ring_prepare(L, Dvec, stats, B * H, Nl, st));
+    }
     B200_CUDA_TRY(cudaMemsetAsync(dQa, 0, acc_bytes, st));
     B200_CUDA_TRY(cudaMemsetAsync(dKa[0], 0, acc_bytes, st));
     B200_CUDA_TRY(cudaMemsetAsync(dVa[0], 0, acc_bytes, st));
@@ -288,40 +502,72 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
     const void* Kc = K; const void* Vc = V;
     int cur = 0;                                       // which fp32 accumulator pair is resident
     for (int step = 0; step < nranks; ++step) {
-        const int slot = step & 1;
-        if (step < nranks - 1) {
-            if (step >= 2) B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[slot], 0));
-            const void* s[2] = {Kc, Vc};
-            void* r[2] = {Kb[slot], Vb[slot]};
-            size_t b[2] = {kv_bytes, kv_bytes};
-            B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
-            B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[slot], rs->comm_stream));
+        const int slot = step & 1, cur_slot = slot ^ 1;
+        if (ce && step >= 1) {
+            const uint32_t k = ++lk.in_kv[cur_slot];
+            B200_TRY(wait_ge(st, lk.flags + F_RDY_KV + cur_slot, k));
+            B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_RDY_KV + cur_slot, k));
         }
-        B200_TRY(b200_fa2_bwd(Q, Kc, Vc, O, L, dO, dQp, dKp, dVp, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st));
-        B200_TRY(accum(dQa, dQp, n_el, dtype, st));
+        if (step < nranks - 1) {
+            if (ce) {
+                B200_TRY(ce_push_kv(lk, rs, slot, Kc, Vc, off(Kb[slot]), off(Vb[slot]), kv_bytes));
+            } else {
+                if (step >= 2) B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[slot], 0));
+                const void* s[2] = {Kc, Vc};
+                void* r[2] = {Kb[slot], Vb[slot]};
+                size_t b[2] = {kv_bytes, kv_bytes};
+                B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[slot], rs->comm_stream));
+            }
+        }
+        if (fused) {
+            B200_TRY(tc_bwd_ring_step(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, Nl, scale == 0.0f ? 1.0f / sqrtf((float)d) : scale, st));
+        } else {
+            B200_TRY(b200_fa2_bwd(Q, Kc, Vc, O, L, dO, dQp, dKp, dVp, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st));
+            B200_TRY(accum(dQa, dQp, n_el, dtype, st));
+        }
         // the running dK/dV of this block arrive from the previous rank while we compute
-        if (step >= 1) B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
+        if (step >= 1) {
+            if (ce) B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
+            else B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
+        }
         B200_TRY(accum(dKa[cur], dKp, n_el, dtype, st));
         B200_TRY(accum(dVa[cur], dVp, n_el, dtype, st));
         // hand the accumulators to the next rank (queued behind this step's K/V prefetch)
         B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
         B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
-        {
+        if (ce) {
+            const int dst = cur ^ 1;
+            // the neighbour's accumulator pair `dst` must have been passed on as often as ours was
+            if (lk.out_acc[dst] > 0) B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_FREE_ACC + dst, lk.out_acc[dst]));
+            B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dKa[dst]), dKa[cur], acc_bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
+            B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dVa[dst]), dVa[cur], acc_bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
+            B200_TRY(write_val(rs->comm_stream, lk.next_flags + F_RDY_ACC + dst, ++lk.push_acc[dst]));
+            B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_ACC + cur, ++lk.out_acc[cur]));
+            if (step >= 1)      // this step's K/V block (compute + onward push both ordered before this point) is released too
+                B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
+        } else {
             const void* s[2] = {dKa[cur], dVa[cur]};
             void* r[2] = {dKa[cur ^ 1], dVa[cur ^ 1]};
             size_t b[2] = {acc_bytes, acc_bytes};
             B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
+            B200_CUDA_TRY(cudaEventRecord(rs->ev_acc, rs->comm_stream));
         }
-        B200_CUDA_TRY(cudaEventRecord(rs->ev_acc, rs->comm_stream));
         cur ^= 1;
-        if (step < nranks - 1) {
+        if (!ce && step < nranks - 1) {
             B200_CUDA_TRY(cudaEventRecord(rs->ev_compute[slot ^ 1], st));
             B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[slot], 0));
-            Kc = Kb[slot]; Vc = Vb[slot];
         }
+        if (step < nranks - 1) { Kc = Kb[slot]; Vc = Vb[slot]; }
     }
-    B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
-    // after P hops the accumulators of block `rank` are back home
+    // after P hops the accumulators of block `rank` are back home (in pair `cur`)
+    if (ce) {
+        B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
+        B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
+        B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
+    } else {
+        B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
+    }
     B200_TRY(cast_out(dQ, dQa, n_el, dtype, st));
     B200_TRY(cast_out(dK, dKa[cur], n_el, dtype, st));
     B200_TRY(cast_out(dV, dVa[cur], n_el, dtype, st));
