@@ -32,6 +32,8 @@ struct RingState {
     cudaEvent_t ev_comm[2] = {nullptr, nullptr};
     cudaEvent_t ev_compute[2] = {nullptr, nullptr};
     cudaEvent_t ev_acc = nullptr;           // ring backward: accumulator hop finished
+    cudaStream_t attn_stream[2] = {nullptr, nullptr};   // ring forward: steps alternate between two streams so the
+    cudaEvent_t ev_attn[2] = {nullptr, nullptr}, ev_merge[2] = {nullptr, nullptr};        // next step's CTAs fill the SMs the current step's last wave leaves idle
     void* buf = nullptr;                    // cached scratch
     size_t bytes = 0;
 };
@@ -52,6 +54,9 @@ static int ring_state(RingState** out)
         for (int i = 0; i < 2; ++i) {
             B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_comm[i], cudaEventDisableTiming));
             B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_compute[i], cudaEventDisableTiming));
+            B200_CUDA_TRY(cudaStreamCreateWithFlags(&s.attn_stream[i], cudaStreamNonBlocking));
+            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_attn[i], cudaEventDisableTiming));
+            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_merge[i], cudaEventDisableTiming));
         }
     }
     *out = &s;
@@ -363,8 +368,8 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t kv_bytes = (size_t)B * H * Nl * d * es;
     const size_t l_bytes = (size_t)B * H * Nl * sizeof(float);
-    // scratch: 2 x (K,V) receive buffers + partial O + partial LSE
-    const size_t total = 4 * align256(kv_bytes) + align256(kv_bytes) + align256(l_bytes);
+    // scratch: 2 x (K,V) receive buffers + 2 x (partial O + partial LSE)
+    const size_t total = 4 * align256(kv_bytes) + 2 * (align256(kv_bytes) + align256(l_bytes));
     void* base;
     bool ce = false;
     B200_TRY(link_prepare(rs, comm, rank, nranks, total, &base, &ce));
@@ -377,22 +382,33 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
         offK[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Kb[i] = p; p += align256(kv_bytes);
         offV[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Vb[i] = p; p += align256(kv_bytes);
     }
-    void* Op = p; p += align256(kv_bytes);
-    float* Lp = reinterpret_cast<float*>(p);
+    void* Opb[2]; float* Lpb[2];
+    for (int i = 0; i < 2; ++i) {
+        Opb[i] = p; p += align256(kv_bytes);
+        Lpb[i] = reinterpret_cast<float*>(p); p += align256(l_bytes);
+    }
 
     const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
-    // the side stream may start once everything already enqueued on the caller's stream is done
+    // the side streams may start once everything already enqueued on the caller's stream is done
     B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
     B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+    if (ce) {
+        B200_CUDA_TRY(cudaStreamWaitEvent(rs->attn_stream[0], rs->ev_main, 0));
+        B200_CUDA_TRY(cudaStreamWaitEvent(rs->attn_stream[1], rs->ev_main, 0));
+    }
 
     const void* Kc = K; const void* Vc = V;
     for (int step = 0; step < nranks; ++step) {
         const int slot = step & 1;            // receive slot for the block used at step+1
         const int cur_slot = slot ^ 1;        // slot holding the block of this step (step >= 1)
+        // copy-engine mode: the attention of consecutive steps runs on two alternating streams (the merges stay
+        // on the caller's stream), so a step's last, partly filled wave overlaps the next step's first one
+        cudaStream_t as = ce ? rs->attn_stream[step & 1] : st;
+        void* Op = Opb[step & 1]; float* Lp = Lpb[step & 1];
         if (ce && step >= 1) {
             // the block of this step was pushed into cur_slot by the previous rank: both streams wait for it
             const uint32_t k = ++lk.in_kv[cur_slot];
-            B200_TRY(wait_ge(st, lk.flags + F_RDY_KV + cur_slot, k));
+            B200_TRY(wait_ge(as, lk.flags + F_RDY_KV + cur_slot, k));
             B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_RDY_KV + cur_slot, k));
         }
         if (step < nranks - 1) {
@@ -409,17 +425,21 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
             }
         }
         // attention of the local queries against the current block (overlaps the exchange above)
-        if (step == 0) {
-            B200_TRY(b200_fa2_fwd(Q, Kc, Vc, O, L, B, H, Nl, Nl, d, scale, dtype, st));
-        } else {
-            B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, st));
+        if (ce && step >= 3) B200_CUDA_TRY(cudaStreamWaitEvent(as, rs->ev_merge[step & 1], 0));   // merge(step-2) has consumed this partial buffer
+        if (step == 0) B200_TRY(b200_fa2_fwd(Q, Kc, Vc, O, L, B, H, Nl, Nl, d, scale, dtype, as));
+        else B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
+        if (ce) {
+            B200_CUDA_TRY(cudaEventRecord(rs->ev_attn[step & 1], as));
+            B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_attn[step & 1], 0));
+        }
+        if (step >= 1) {
             B200_TRY(b200_lse_merge(O, L, Op, Lp, B, H, Nl, d, dtype, st));
+            if (ce) B200_CUDA_TRY(cudaEventRecord(rs->ev_merge[step & 1], st));           // partial buffer (step & 1) is free again
         }
         if (ce) {
             if (step >= 1) {
                 // cur_slot is free again once this step's attention AND its onward push are done: tell the sender
-                B200_CUDA_TRY(cudaEventRecord(rs->ev_compute[cur_slot], st));
-                B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_compute[cur_slot], 0));
+                B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_attn[step & 1], 0));
                 B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
             }
         } else if (step < nranks - 1) {
