@@ -106,3 +106,45 @@ def uses_tensor_cores(dtype, d, Nq, Nkv, backward=False):
     code = B200_DTYPE_F32 if dtype == torch.float32 else B200_DTYPE_BF16
     fn = lib.b200_bwd_uses_tensor_cores if backward else lib.b200_fwd_uses_tensor_cores
     return bool(fn(code, d, Nq, Nkv))
+
+
+def _check_host(*ts):
+    dt = ts[0].dtype
+    for t in ts:
+        if t.is_cuda:
+            raise ValueError("host entry point: tensors must be CPU tensors (pin them for full PCIe speed)")
+        if t.dtype != dt or not t.is_contiguous():
+            raise ValueError("host tensors must share dtype and be contiguous row-major [.., N, d]")
+
+
+def flash_attention_2_forward_host(Q, K, V, softmax_scale=0.0, out=None, device=None):
+    """Host tensors in, host tensors out: (O, L).  What the reference's drivers do around every call
+    (cudaMemcpy H2D, kernel, cudaMemcpy D2H -- src/02_flash_attention_v2_forward/main.cu:42-64), but
+    chunked over the (b,h) slabs with copies and attention overlapped (b200_fa2_fwd_host).
+    Stream-ordered: synchronise the current stream before reading the results."""
+    _check_host(Q, K, V)
+    B, H, N, d = _bhnd(Q)
+    O, L = out if out is not None else (torch.empty_like(Q).pin_memory(),
+                                        torch.empty(Q.shape[:-1], dtype=torch.float32).pin_memory())
+    with torch.cuda.device(device if device is not None else torch.cuda.current_device()):
+        check(lib.b200_fa2_fwd_host(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(),
+                                    B, H, N, d, float(softmax_scale), _dtype_code(Q), _stream()), "b200_fa2_fwd_host")
+    return O, L
+
+
+def flash_attention_2_forward_backward_host(Q, K, V, dO, softmax_scale=0.0, out=None, device=None):
+    """Host tensors in, host tensors out: (O, L, dQ, dK, dV) -- forward and backward of every chunk of
+    (b,h) slabs, pipelined with the PCIe copies in both directions (b200_fa2_fwd_bwd_host; the
+    reference's host-side pattern is src/02_flash_attention_v2_backward/main.cu:261-289)."""
+    _check_host(Q, K, V, dO)
+    B, H, N, d = _bhnd(Q)
+    if out is None:
+        out = tuple(torch.empty_like(Q).pin_memory() for _ in range(1)) + \
+              (torch.empty(Q.shape[:-1], dtype=torch.float32).pin_memory(),) + \
+              tuple(torch.empty_like(Q).pin_memory() for _ in range(3))
+    O, L, dQ, dK, dV = out
+    with torch.cuda.device(device if device is not None else torch.cuda.current_device()):
+        check(lib.b200_fa2_fwd_bwd_host(Q.data_ptr(), K.data_ptr(), V.data_ptr(), dO.data_ptr(), O.data_ptr(), L.data_ptr(),
+                                        dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), B, H, N, d, float(softmax_scale),
+                                        _dtype_code(Q), _stream()), "b200_fa2_fwd_bwd_host")
+    return O, L, dQ, dK, dV

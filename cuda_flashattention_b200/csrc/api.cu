@@ -104,6 +104,95 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
 }
 
+// ---- host-buffer pipeline (b200_fa2_fwd_host / b200_fa2_fwd_bwd_host) ------------------------------
+struct HostPipe {
+    cudaStream_t h2d = nullptr, comp = nullptr, d2h = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    void* buf = nullptr;
+    size_t bytes = 0;
+};
+static HostPipe g_pipe[64];
+static std::mutex g_pipe_mu;
+
+static int host_pipeline(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
+                         void* hdQ, void* hdK, void* hdV, bool do_bwd, int B, int H, int N, int d, float scale,
+                         int dtype, cudaStream_t st)
+{
+    if (!valid_dtype(dtype) || B < 0 || H < 0 || N < 0 || d <= 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    const int BH = B * H;
+    if (BH == 0 || N == 0) return B200_OK;
+    if (!hQ || !hK || !hV || !hO || !hL || (do_bwd && (!hdO || !hdQ || !hdK || !hdV))) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_pipe_mu);
+    HostPipe& P = g_pipe[dev];
+    if (!P.h2d) {
+        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.h2d, cudaStreamNonBlocking));
+        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.comp, cudaStreamNonBlocking));
+        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.d2h, cudaStreamNonBlocking));
+        B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_start, cudaEventDisableTiming));
+        B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_end, cudaEventDisableTiming));
+        for (int i = 0; i < 2; ++i) {
+            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_in[i], cudaEventDisableTiming));
+            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_done[i], cudaEventDisableTiming));
+            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_out[i], cudaEventDisableTiming));
+        }
+    }
+    const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
+    const size_t slab = (size_t)N * d * es, lslab = (size_t)N * sizeof(float);
+    // chunk = as many (b,h) slabs as give ~32 MB per tensor: small enough to pipeline, large enough to fill the GPU
+    int hc = (int)(((size_t)32 << 20) / slab);
+    if (hc < 1) hc = 1;
+    if (hc > BH) hc = BH;
+    const int nchunks = (BH + hc - 1) / hc;
+    const int n_in = do_bwd ? 4 : 3, n_out = do_bwd ? 4 : 1;
+    const size_t tb = (((size_t)hc * slab) + 255) & ~(size_t)255, lb = (((size_t)hc * lslab) + 255) & ~(size_t)255;
+    const size_t per_set = (size_t)(n_in + n_out) * tb + lb;
+    const size_t need = 2 * per_set;
+    if (P.bytes < need) {
+        if (P.buf) { B200_CUDA_TRY(cudaDeviceSynchronize()); B200_CUDA_TRY(cudaFree(P.buf)); P.buf = nullptr; P.bytes = 0; }
+        B200_CUDA_TRY(cudaMalloc(&P.buf, need));
+        P.bytes = need;
+    }
+    B200_CUDA_TRY(cudaEventRecord(P.ev_start, st));
+    B200_CUDA_TRY(cudaStreamWaitEvent(P.h2d, P.ev_start, 0));
+    B200_CUDA_TRY(cudaStreamWaitEvent(P.d2h, P.ev_start, 0));
+    const uint8_t* hin[4] = {(const uint8_t*)hQ, (const uint8_t*)hK, (const uint8_t*)hV, (const uint8_t*)hdO};
+    uint8_t* hout[4] = {(uint8_t*)hO, (uint8_t*)hdQ, (uint8_t*)hdK, (uint8_t*)hdV};
+    for (int c = 0; c < nchunks; ++c) {
+        const int b = c & 1, h0 = c * hc, nh = (BH - h0) < hc ? (BH - h0) : hc;
+        uint8_t* base = reinterpret_cast<uint8_t*>(P.buf) + (size_t)b * per_set;
+        uint8_t* din[4]; uint8_t* dout[4];
+        for (int i = 0; i < 4; ++i) { din[i] = base + (size_t)i * tb; dout[i] = base + (size_t)(n_in + i) * tb; }
+        float* dL = reinterpret_cast<float*>(base + (size_t)(n_in + n_out) * tb);
+        // host -> device (the input set b is free once the compute of the chunk that used it last -- chunk c-2, or a
+        // chunk of the previous call, which may still be in flight on these streams -- is done)
+        B200_CUDA_TRY(cudaStreamWaitEvent(P.h2d, P.ev_done[b], 0));
+        for (int i = 0; i < n_in; ++i)
+            B200_CUDA_TRY(cudaMemcpyAsync(din[i], hin[i] + (size_t)h0 * slab, (size_t)nh * slab, cudaMemcpyHostToDevice, P.h2d));
+        B200_CUDA_TRY(cudaEventRecord(P.ev_in[b], P.h2d));
+        // attention (the output set b is free once chunk c-2 has been copied out)
+        B200_CUDA_TRY(cudaStreamWaitEvent(P.comp, P.ev_in[b], 0));
+        B200_CUDA_TRY(cudaStreamWaitEvent(P.comp, P.ev_out[b], 0));
+        B200_TRY(fwd_impl(din[0], din[1], din[2], dout[0], dL, nh, N, N, d, scale, dtype, P.comp));
+        if (do_bwd)
+            B200_TRY(bwd_impl(din[0], din[1], din[2], dout[0], dL, din[3], dout[1], dout[2], dout[3], nh, N, N, d, scale, dtype,
+                              nullptr, 0, P.comp));
+        B200_CUDA_TRY(cudaEventRecord(P.ev_done[b], P.comp));
+        // device -> host
+        B200_CUDA_TRY(cudaStreamWaitEvent(P.d2h, P.ev_done[b], 0));
+        for (int i = 0; i < n_out; ++i)
+            B200_CUDA_TRY(cudaMemcpyAsync(hout[i] + (size_t)h0 * slab, dout[i], (size_t)nh * slab, cudaMemcpyDeviceToHost, P.d2h));
+        B200_CUDA_TRY(cudaMemcpyAsync(hL + (size_t)h0 * N, dL, (size_t)nh * lslab, cudaMemcpyDeviceToHost, P.d2h));
+        B200_CUDA_TRY(cudaEventRecord(P.ev_out[b], P.d2h));
+    }
+    B200_CUDA_TRY(cudaEventRecord(P.ev_end, P.d2h));
+    B200_CUDA_TRY(cudaStreamWaitEvent(st, P.ev_end, 0));
+    return B200_OK;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -165,6 +254,14 @@ int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L,
     if (B < 0 || H < 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
     return fwd_impl(Q, K, V, O, L, B * H, Nq, Nkv, d, scale, dtype, st);
 }
+
+int b200_fa2_fwd_host(const void* hQ, const void* hK, const void* hV, void* hO, float* hL,
+                      int B, int H, int N, int d, float scale, int dtype, cudaStream_t st)
+{ return host_pipeline(hQ, hK, hV, nullptr, hO, hL, nullptr, nullptr, nullptr, false, B, H, N, d, scale, dtype, st); }
+
+int b200_fa2_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
+                          void* hdQ, void* hdK, void* hdV, int B, int H, int N, int d, float scale, int dtype, cudaStream_t st)
+{ return host_pipeline(hQ, hK, hV, hdO, hO, hL, hdQ, hdK, hdV, true, B, H, N, d, scale, dtype, st); }
 
 size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
 {

@@ -105,6 +105,22 @@ B200_API int b200_fa1_fwd_f32(const float* Q, const float* K, const float* V, fl
 B200_API int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L,
                  int B, int H, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t stream);
 
+/* ---- host-buffer entry points --------------------------------------------------------------------
+ * The reference's drivers own HOST arrays and copy them to the device around every call
+ * (src/02_flash_attention_v2_forward/main.cu:42-64, src/02_flash_attention_v2_backward/main.cu:261-289).
+ * These do the same job for [B,H,N,d] host tensors (pinned memory for full speed), but pipelined:
+ * the (b,h) slabs are cut into chunks and host->device copies, attention and device->host copies
+ * of consecutive chunks overlap on three internal streams, so the call runs at PCIe speed instead
+ * of copy + compute + copy.  Stream-ordered on `stream` (not host-synchronous); the host buffers
+ * must stay valid until `stream` has passed the call.
+ *   b200_fa2_fwd_host     : O, L              <- Q, K, V
+ *   b200_fa2_fwd_bwd_host : O, L, dQ, dK, dV  <- Q, K, V, dO   (forward + backward of every chunk) */
+B200_API int b200_fa2_fwd_host(const void* hQ, const void* hK, const void* hV, void* hO, float* hL,
+                      int B, int H, int N, int d, float scale, int dtype, cudaStream_t stream);
+B200_API int b200_fa2_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO,
+                          void* hO, float* hL, void* hdQ, void* hdK, void* hdV,
+                          int B, int H, int N, int d, float scale, int dtype, cudaStream_t stream);
+
 /* Workspace the batched backward needs (D vector and, on the tensor-core path, an fp32 dQ
  * accumulator).  Pass workspace = NULL to let the library use its internal arena. */
 B200_API size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype);
