@@ -56,6 +56,27 @@ def peaks():
     return {"src": "fallback", "burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0}
 
 
+def ncu_traffic(kernel_substr):
+    """DRAM bytes (read + write) of one launch of the dominant kernel, from the committed `ncu --set full` capture of
+    the same C3 workload (profiles/, see its README); None when the summary is not there."""
+    import csv
+    best = None
+    for name in sorted(os.listdir(os.path.join(ROOT, "profiles"))) if os.path.isdir(os.path.join(ROOT, "profiles")) else []:
+        if not (name.endswith(".csv") and "ncu_full" in name):
+            continue
+        try:
+            rows = list(csv.reader(open(os.path.join(ROOT, "profiles", name))))
+            hdr, units = rows[0], rows[1]
+            ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+            mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            for r in rows[2:]:
+                if kernel_substr in r[ik]:
+                    best = {"bytes": float(r[ir]) * mult.get(units[ir], 1.0) + float(r[iw]) * mult.get(units[iw], 1.0), "src": "profiles/" + name}
+        except Exception:
+            continue
+    return best
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons during the timed region (NVML)."""
 
@@ -299,6 +320,12 @@ def run_ours(args):
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        if world == 1:
+            tr = ncu_traffic("bwd_kernel" if dom == "bwd" else "fwd_kernel")
+            if tr:
+                line["roofline"]["traffic"] = tr["bytes"]
+                line["roofline"]["traffic_note"] = (f"DRAM read+write bytes of one {dom}_kernel launch at this workload, ncu --set full, {tr['src']}; "
+                                                    f"algorithmic bytes {'2.15e9' if dom == 'bwd' else '1.07e9'}")
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line))
