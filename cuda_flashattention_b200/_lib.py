@@ -34,6 +34,8 @@ _SIGS = {
     "b200_fa2_bwd_f32": (_i, [_vp] * 9 + [_i, _i, _f, _vp]),
     "b200_fa1_fwd_f32": (_i, [_vp] * 6 + [_i, _i, _vp]),
     "b200_fa2_fwd": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b200_fa2_fwd_ex": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _i, _f, _i, _i, _vp]),
+    "b200_fa2_bwd_ex": (_i, [_vp] * 9 + [_i, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
     "b200_fa2_fwd_host": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),

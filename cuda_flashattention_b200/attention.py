@@ -17,6 +17,8 @@ import torch
 
 from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32
 
+FLAG_CAUSAL = 1  # B200_FLAG_CAUSAL (include/b200attn.h)
+
 
 def _dtype_code(t):
     if t.dtype == torch.float32:
@@ -49,7 +51,9 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
-def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True):
+def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True, causal=False):
+    """O, L = FA2 forward.  causal=True (an extension, the reference is non-causal) hides key j from query i
+    when j > i + (Nkv - Nq)."""
     _check_inputs(Q, K, V)
     B, H, Nq, d = _bhnd(Q)
     Bk, Hk, Nkv, dk = _bhnd(K)
@@ -58,12 +62,13 @@ def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True):
     O = torch.empty_like(Q)
     L = torch.empty(Q.shape[:-1], dtype=torch.float32, device=Q.device)
     with torch.cuda.device(Q.device):
-        check(lib.b200_fa2_fwd(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(),
-                               B, H, Nq, Nkv, d, float(softmax_scale), _dtype_code(Q), _stream()), "b200_fa2_fwd")
+        check(lib.b200_fa2_fwd_ex(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(),
+                                  B, H, Nq, Nkv, d, float(softmax_scale), _dtype_code(Q), FLAG_CAUSAL if causal else 0,
+                                  _stream()), "b200_fa2_fwd_ex")
     return (O, L) if return_lse else O
 
 
-def flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale=0.0):
+def flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale=0.0, causal=False):
     _check_inputs(Q, K, V, O, dO)
     B, H, Nq, d = _bhnd(Q)
     _, _, Nkv, _ = _bhnd(K)
@@ -71,9 +76,9 @@ def flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale=0.0):
         raise ValueError("L must be contiguous fp32")
     dQ, dK, dV = torch.empty_like(Q), torch.empty_like(K), torch.empty_like(V)
     with torch.cuda.device(Q.device):
-        check(lib.b200_fa2_bwd(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(), dO.data_ptr(),
-                               dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), B, H, Nq, Nkv, d, float(softmax_scale),
-                               _dtype_code(Q), None, 0, _stream()), "b200_fa2_bwd")
+        check(lib.b200_fa2_bwd_ex(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(), dO.data_ptr(),
+                                  dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), B, H, Nq, Nkv, d, float(softmax_scale),
+                                  _dtype_code(Q), FLAG_CAUSAL if causal else 0, None, 0, _stream()), "b200_fa2_bwd_ex")
     return dQ, dK, dV
 
 

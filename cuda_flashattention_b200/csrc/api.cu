@@ -63,16 +63,20 @@ static inline bool valid_dtype(int dt) { return dt == B200_DTYPE_BF16 || dt == B
 static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sqrtf((float)d) : s; }
 
 static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
-                    float scale, int dtype, cudaStream_t st)
+                    float scale, int dtype, cudaStream_t st, int flags = 0)
 {
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
+    if ((flags & ~B200_FLAG_CAUSAL) != 0 || (causal && Nq > Nkv)) return B200_ERR_INVALID_ARGUMENT;
     if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (BH == 0 || Nq == 0) return B200_OK;
     if (Nkv == 0) return B200_ERR_INVALID_ARGUMENT;            // softmax over an empty set is undefined
     if (!Q || !K || !V || !O) return B200_ERR_INVALID_ARGUMENT;
     B200_TRY(device_check());
     scale = resolve_scale(scale, d);
-    if (!g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv)) return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st);
-    return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
+    // tensor-core causal path: square problems (the usual self-attention case); everything else runs on the generic kernels
+    if (!g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv))
+        return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st, causal);
+    return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
 }
 
 static size_t bwd_ws_bytes(int BH, int Nq, int Nkv, int d, int dtype)
@@ -84,8 +88,10 @@ static size_t bwd_ws_bytes(int BH, int Nq, int Nkv, int d, int dtype)
 
 static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
                     void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
-                    void* ws, size_t ws_bytes, cudaStream_t st)
+                    void* ws, size_t ws_bytes, cudaStream_t st, int flags = 0)
 {
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
+    if ((flags & ~B200_FLAG_CAUSAL) != 0 || (causal && Nq > Nkv)) return B200_ERR_INVALID_ARGUMENT;
     if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (BH == 0 || (Nq == 0 && Nkv == 0)) return B200_OK;
     if (Nq == 0 || Nkv == 0) return B200_ERR_INVALID_ARGUMENT;
@@ -98,10 +104,10 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     float* D = reinterpret_cast<float*>(ws);
     const size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
     B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
-    if (!g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv))
+    if (!g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv))
         return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
-                      reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
-    return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
+                      reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st, causal);
+    return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
 }
 
 // ---- host-buffer pipeline (b200_fa2_fwd_host / b200_fa2_fwd_bwd_host) ------------------------------
@@ -262,6 +268,21 @@ int b200_fa2_fwd_host(const void* hQ, const void* hK, const void* hV, void* hO, 
 int b200_fa2_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
                           void* hdQ, void* hdK, void* hdV, int B, int H, int N, int d, float scale, int dtype, cudaStream_t st)
 { return host_pipeline(hQ, hK, hV, hdO, hO, hL, hdQ, hdK, hdV, true, B, H, N, d, scale, dtype, st); }
+
+int b200_fa2_fwd_ex(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nq, int Nkv, int d,
+                    float scale, int dtype, int flags, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    return fwd_impl(Q, K, V, O, L, B * H, Nq, Nkv, d, scale, dtype, st, flags);
+}
+
+int b200_fa2_bwd_ex(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                    void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype, int flags,
+                    void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    if (B < 0 || H < 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    return bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, B * H, Nq, Nkv, d, scale, dtype, ws, ws_bytes, st, flags);
+}
 
 size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
 {

@@ -72,14 +72,15 @@ __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
 // a load issued on the critical path queues behind operand traffic for hundreds of cycles.
 __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* smem, uint64_t* bar_in_full,
                                                  uint64_t* bar_S, uint64_t* bar_dP, uint64_t* bar_P, uint64_t* bar_dS,
-                                                 int n_q, float scale_log2, float scale)
+                                                 int n_it, int qt_min, int i_off, int kv0, int causal,
+                                                 float scale_log2, float scale)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // kv row within the tile == TMEM lane
     const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
     const bool lane0 = (threadIdx.x & 31) == 0;
     const uint32_t stat_base = smem_u32(smem + OFF_STAT) + 128 * w;    // + s * 2 * STAT_BYTES (+ STAT_BYTES for D)
-    for (int i = 0; i < n_q; ++i) {
+    for (int i = 0; i < n_it; ++i) {
         const int b = i & 1, s = i % NS;
         const uint32_t tS = tmem + TM_S + 64 * b + 32 * w + lane_base;
         const uint32_t tP = tmem + TM_DP + 32 * w + lane_base;
@@ -98,6 +99,16 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         float p[32];
 #pragma unroll
         for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
+        if (causal) {
+            // key kv0 + r is hidden from the queries before it: only the two q tiles on the diagonal are affected
+            int qt = i + i_off;
+            if (qt >= n_it) qt -= n_it;
+            const int first_visible = kv0 + r - (qt_min + qt) * BM - 32 * w;   // column (of this warpgroup's 32) of query kv0 + r
+            if (first_visible > 0) {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) if (c < first_visible) p[c] = 0.0f;
+            }
+        }
         {
             uint32_t pk[16];
 #pragma unroll
@@ -145,15 +156,17 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
 // into the dQ accumulator.  A warp's 32 lanes hold 32 consecutive d of one q row, so every red
 // instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
-                                               float* __restrict__ dQacc, int Nq, int n_q, int i_off, int bh, int dbg)
+                                               float* __restrict__ dQacc, int Nq, int n_it, int qt_min, int i_off, int bh,
+                                               int dbg)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
     const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
     const bool lane0 = (threadIdx.x & 31) == 0;
-    for (int i = 0; i < n_q; ++i) {
+    for (int i = 0; i < n_it; ++i) {
         int qt = i + i_off;                                            // the q tile this iteration works on
-        if (qt >= n_q) qt -= n_q;
+        if (qt >= n_it) qt -= n_it;
+        qt += qt_min;
         mbar_wait(bar_dQ_full, i & 1);
         tc_fence_after();
         B200_TRB(1, i, 0);
@@ -218,7 +231,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
            float* __restrict__ dQacc, const __grid_constant__ CUtensorMap tmdK,
            const __grid_constant__ CUtensorMap tmdV, const float* __restrict__ L2p, const float* __restrict__ Dp,
-           int Nq, int Nq_pad, float scale_log2, float scale, int dbg)
+           int Nq, int Nq_pad, float scale_log2, float scale, int dbg, int causal)
 {
     using namespace bwd;
     extern __shared__ uint8_t smem_raw[];
@@ -242,7 +255,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     // Every CTA of a (b,h) slab walks the q tiles in the same cyclic order but starts at a different
     // one: at any moment the CTAs that run together reduce-add into DIFFERENT dQ tiles, so their
     // fp32 atomics do not queue up on the same L2 lines.
-    const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x);
+    // Causal (Nq == Nkv): the q tiles before the diagonal (rows < kv0) see none of this CTA's keys and are skipped;
+    // low blockIdx.x = most work = scheduled first.
+    const int qt_min = causal ? min(kv0 / BM, n_q - 1) : 0;
+    const int n_it = n_q - qt_min;
+    const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x) % n_it;
 
     if (threadIdx.x == 0) {
         mbar_init(bar_KV, 1);
@@ -270,10 +287,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             }
             const float* Lrow = L2p + (size_t)bh * Nq_pad;
             const float* Drow = Dp + (size_t)bh * Nq_pad;
-            for (int i = 0; i < n_q; ++i) {
+            for (int i = 0; i < n_it; ++i) {
                 const int s = i % NS;
                 int qt = i + i_off;
-                if (qt >= n_q) qt -= n_q;
+                if (qt >= n_it) qt -= n_it;
+                qt += qt_min;
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
                 mbar_expect_tx(&bar_in_full[s], 2 * Q_TILE + 2 * STAT_BYTES);
                 for (int b = 0; b < 2; ++b) {
@@ -312,9 +330,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             mbar_wait(&bar_in_full[0], 0);
             tc_fence_after();
             M1(0); M2(0);
-            for (int i = 0; i < n_q; ++i) {
+            for (int i = 0; i < n_it; ++i) {
                 const int b = i & 1, s = i % NS;
-                if (i + 1 < n_q) {
+                if (i + 1 < n_it) {
                     mbar_wait(&bar_in_full[(i + 1) % NS], ((i + 1) / NS) & 1);
                     tc_fence_after();
                     M1(i + 1);
@@ -330,7 +348,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 B200_TRB(2, i, 3);
                 mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
                 umma_commit(&bar_in_empty[s]);
-                if (i + 1 < n_q) M2(i + 1);
+                if (i + 1 < n_it) M2(i + 1);
                 B200_TRB(2, i, 4);
                 mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
                 tc_fence_after();
@@ -349,12 +367,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         }
     } else if (warp >= 4 && warp < 12) {
         const int w = (warp - 4) >> 2;
-        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_q, scale_log2, scale);
+        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_it, qt_min, i_off, kv0, causal, scale_log2, scale);
         mbar_wait(bar_done, 0);
         tc_fence_after();
         bwd_epilogue(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
     } else if (warp >= 12) {
-        bwd_drain_role(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_q, i_off, bh, dbg);
+        bwd_drain_role(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_it, qt_min, i_off, bh, dbg);
     }
 
     tc_fence_before();
@@ -415,7 +433,8 @@ size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
 }
 
 static int bwd_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
-                      float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st)
+                      float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st,
+                      bool causal = false)
 {
     using namespace bwd;
     static bool attr_set = false;
@@ -434,7 +453,7 @@ static int bwd_launch(const void* Q, const void* K, const void* V, const void* d
     static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
     if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
     bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
-                                            scale * 1.4426950408889634f, scale, dbg);
+                                            scale * 1.4426950408889634f, scale, dbg, causal ? 1 : 0);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
@@ -442,12 +461,13 @@ static int bwd_launch(const void* Q, const void* K, const void* V, const void* d
 
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* Dvec,
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
-           void* ws, size_t ws_bytes, cudaStream_t st)
+           void* ws, size_t ws_bytes, cudaStream_t st, bool causal)
 {
     using namespace bwd;
+    if (causal && Nq != Nkv) return B200_ERR_UNSUPPORTED;
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
     if ((align & 15) != 0 || BH > 65535)
-        return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st);
+        return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
     if (ws_bytes < tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype)) return B200_ERR_WORKSPACE;
     const int Nq_pad = (Nq + 63) / 64 * 64;
     uint8_t* p = reinterpret_cast<uint8_t*>(ws);
@@ -461,7 +481,7 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
-    B200_TRY(bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st));
+    B200_TRY(bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
     unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
     if (cgrid > 148u * 8) cgrid = 148u * 8;
     cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);

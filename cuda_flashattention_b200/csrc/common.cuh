@@ -27,25 +27,30 @@ void count_launch(int n = 1);       // bookkeeping for b200_debug_launch_count()
         if (s__ != B200_OK) return s__;                       \
     } while (0)
 
+// Causal masking (extension; the reference is non-causal): key j is visible to query i iff j - i <= coff, with
+// coff = Nkv - Nq (bottom-right aligned) when causal and kNoCausal otherwise.
+constexpr int kNoCausal = 0x3fffffff;
+
 // ---- generic CUDA-core kernels (generic_simt.cu) ------------------------------------------------
 // mode 0: O + LSE (L may be NULL);  mode 1: O + l (into L) + m (into M)   [FA1 API]
 int simt_fwd(const void* Q, const void* K, const void* V, void* O, float* L, float* M, int BH, int Nq, int Nkv, int d,
-             float scale, int dtype, int mode, cudaStream_t st);
+             float scale, int dtype, int mode, cudaStream_t st, int coff = kNoCausal);
 int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtype, cudaStream_t st);
 // dQ may be NULL (skip), or dK and dV both NULL (skip)
 int simt_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
-             void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st);
+             void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st,
+             int coff = kNoCausal);
 int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st);
 
 // ---- tcgen05 tensor-core kernels (fwd_sm100.cu / bwd_sm100.cu) ------------------------------------
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv);
 int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
-           float scale, int dtype, cudaStream_t st);
+           float scale, int dtype, cudaStream_t st, bool causal = false);
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
-           void* ws, size_t ws_bytes, cudaStream_t st);
+           void* ws, size_t ws_bytes, cudaStream_t st, bool causal = false);
 
 // ring backward building blocks (bf16, d = 128): padded statistics once, then accumulate-only steps
 bool tc_bwd_ring_supported(int dtype, int d, int BH, const void* Q, const void* K, const void* V, const void* dO);

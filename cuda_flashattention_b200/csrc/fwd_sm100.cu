@@ -47,7 +47,9 @@ struct FwdCfg {
     static constexpr int POLY = POLY_;
     static constexpr bool SPLITP = SPLITP_;
     static constexpr int NBARS = NT * 5 + STAGES * 4;
-    static constexpr int REGS_CTRL = 64, REGS_SOFTMAX = 216;   // setmaxnreg targets (warps 0-3 / softmax)
+    // setmaxnreg targets (warps 0-3 / softmax).  The pool is what the CTA got at launch -- 384 threads x 168
+    // registers = 64512, not the whole 64K file -- and a setmaxnreg.inc that cannot be served waits forever.
+    static constexpr int REGS_CTRL = 64, REGS_SOFTMAX = 216;
     static constexpr int SMEM = 1024 + NT * Q_TILE + 2 * STAGES * KV_TILE + NBARS * 8 + 16;
     static constexpr int PCOLS_PER_CHUNK = kF32 ? 32 : 16;   // TMEM columns written per 32 P values
     // V is the MN-major B operand of O += P V.  bf16: plain 128B swizzle.  tf32: the hardware only
@@ -56,7 +58,7 @@ struct FwdCfg {
     static constexpr uint32_t V_SBO = kF32 ? 512u : 1024u;
     static_assert(D % CPB == 0 && BC % 64 == 0 && BC <= 128 && D <= 128, "tile shape");
     static_assert(POLY == 0 || !kF32, "the polynomial exp2 is only accurate enough for bf16 P");
-    static_assert(128 * REGS_CTRL + 256 * REGS_SOFTMAX <= 65536, "register file");
+    static_assert(NT != 2 || 128 * REGS_CTRL + 256 * REGS_SOFTMAX <= 384 * 168, "register pool of the CTA");
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
 };
 
@@ -84,8 +86,8 @@ constexpr float kRescaleThreshold = 8.0f;
 template <class C>
 __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, uint64_t* bar_S, uint64_t* bar_Pa,
                                              uint64_t* bar_Pb, uint64_t* bar_O, const CUtensorMap* tmO,
-                                             float* __restrict__ Lout, int Nq, int Nkv, int nkv, int q0, int bh,
-                                             float scale_log2)
+                                             float* __restrict__ Lout, int Nq, int Nkv, int nkv, int n_plain,
+                                             int causal, int q0, int bh, float scale_log2)
 {
     constexpr int BC = C::BC, D = C::D;
     const int wg_thread = threadIdx.x & 127;                       // == TMEM lane == row within the tile
@@ -93,12 +95,13 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     const uint32_t lane_base = uint32_t(warp_in_wg * 32) << 16;
     const uint32_t tS = tmem + 128 * t + lane_base;                // S_t and (aliased) P_t
     const uint32_t tO = tmem + 256 + 128 * t + lane_base;
-    const int tail = Nkv - (nkv - 1) * BC;                         // valid columns in the last K/V tile
+    // first key column this row must NOT see: Nkv (ragged last tile), and row + 1 under the causal mask
+    const int col_end = causal ? min(Nkv, q0 + t * 128 + wg_thread + 1) : Nkv;
     const uint64_t scale2 = f2_pack(scale_log2, scale_log2);
 
     float m = -INFINITY, l = 0.0f;                                 // m in log2 units (already scaled)
 
-    // one K/V tile: S_t(j) -> (m, l) update -> P_t(j).  kMasked = the ragged last tile.
+    // one K/V tile: S_t(j) -> (m, l) update -> P_t(j).  kMasked = the ragged last tile / the causal diagonal tiles.
     auto step = [&](auto masked_tag, const int j) {
         constexpr bool kMasked = decltype(masked_tag)::value;
         mbar_wait(bar_S, j & 1);
@@ -110,8 +113,9 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
         tmem_wait_ld();
         B200_TR(t, j, 1);
         if constexpr (kMasked) {
+            const int lim = col_end - j * BC;
 #pragma unroll
-            for (int i = 0; i < BC; ++i) if (i >= tail) s[i] = 0xff800000u;      // -inf
+            for (int i = 0; i < BC; ++i) if (i >= lim) s[i] = 0xff800000u;       // -inf
         }
         // P for chunks [32 c0, 32 c1) of the row with the running max m; partial row sums into acc
         uint64_t acc[4];
@@ -195,8 +199,8 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
         B200_TR(t, j, 7);
     };
 
-    for (int j = 0; j < nkv - 1; ++j) step(std::false_type{}, j);
-    step(std::true_type{}, nkv - 1);                               // (a full last tile masks nothing)
+    for (int j = 0; j < n_plain; ++j) step(std::false_type{}, j);
+    for (int j = n_plain; j < nkv; ++j) step(std::true_type{}, j); // (a full last tile masks nothing)
 
     // ---- epilogue: O_t / l -> smem (reusing the Q tile, 128B-swizzled) -> TMA store; LSE -> global
     mbar_wait(bar_O, 0);
@@ -250,7 +254,7 @@ template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-           float* __restrict__ Lout, int Nq, int Nkv, float scale_log2)
+           float* __restrict__ Lout, int Nq, int Nkv, float scale_log2, int causal)
 {
     constexpr int NT = C::NT, BC = C::BC, D = C::D, ST = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -272,9 +276,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 
     const int warp = threadIdx.x >> 5;
     const int bh = blockIdx.y;
-    const int q0 = blockIdx.x * (NT * 128);
+    // causal (Nq == Nkv): the q blocks near the end of the sequence have the most K/V tiles -- schedule them first
+    const int q0 = (causal ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * (NT * 128);
     const int ntiles = min(NT, (Nq - q0 + 127) / 128);
-    const int nkv = (Nkv + BC - 1) / BC;
+    const int nkv_all = (Nkv + BC - 1) / BC;
+    // K/V tiles that query tile t needs (rows q0 + 128 t .. + 127 see keys 0 .. row), and for the whole CTA
+    auto nkv_of = [&](int t) { return causal ? min(nkv_all, (q0 + t * 128 + 127) / BC + 1) : nkv_all; };
+    const int nkv = nkv_of(ntiles - 1), nkv_first = nkv_of(0);
 
     if (threadIdx.x == 0) {
         for (int t = 0; t < NT; ++t) { mbar_init(&bar_Q[t], 1); mbar_init(&bar_S[t], 1); mbar_init(&bar_Pa[t], 4); mbar_init(&bar_Pb[t], 4); mbar_init(&bar_O[t], 1); }
@@ -357,6 +365,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 mbar_wait(&bar_Vf[s], (j / ST) & 1);
                 if (j + 1 < nkv) mbar_wait(&bar_Kf[(j + 1) % ST], ((j + 1) / ST) & 1);
                 for (int t = 0; t < ntiles; ++t) {
+                    const int nkv_t = (t == ntiles - 1) ? nkv : nkv_first;   // (NT <= 2)
+                    if (j >= nkv_t) continue;
                     if (C::SPLITP) {
                         mbar_wait(&bar_Pa[t], j & 1);
                         tc_fence_after();
@@ -368,7 +378,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                     if (!C::SPLITP) issue_PV(t, j, 0);
                     issue_PV(t, j, 1);
                     if (t == ntiles - 1) umma_commit(&bar_Ve[s]);
-                    if (j + 1 < nkv) {
+                    if (j + 1 < nkv_t) {
                         issue_S(t, j + 1);
                         if (t == ntiles - 1) umma_commit(&bar_Ke[(j + 1) % ST]);
                     } else {
@@ -384,7 +394,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         // ================================ softmax warpgroups ==========================
         if constexpr (NT == 2) reg_inc<C::REGS_SOFTMAX>();
         const int t = (warp - 4) >> 2;
-        if (t < ntiles) softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv, q0, bh, scale_log2);
+        if (t < ntiles) {
+            const int nkv_t = nkv_of(t);
+            // tiles entirely below the diagonal (and not the ragged last one) need no mask
+            const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + 1) / BC, Nkv / BC)) : nkv_t - 1;
+            softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv_t, n_plain,
+                            causal, q0, bh, scale_log2);
+        }
     }
 
     tc_fence_before();
@@ -395,7 +411,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 // ------------------------------------------------------------------------------------ host side
 template <class C>
 static int launch_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv,
-                      float scale, cudaStream_t st)
+                      float scale, cudaStream_t st, bool causal)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -415,7 +431,7 @@ static int launch_fwd(const void* Q, const void* K, const void* V, void* O, floa
             make_tmap_3d(&tmO, (uint8_t*)O + qoff, dt, C::EB, nbh, Nq, C::D, 128, C::CPB))
             return B200_ERR_CUDA;
         dim3 grid((Nq + C::NT * 128 - 1) / (C::NT * 128), nbh);
-        fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, L ? L + (size_t)bh0 * Nq : nullptr, Nq, Nkv, scale_log2);
+        fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, L ? L + (size_t)bh0 * Nq : nullptr, Nq, Nkv, scale_log2, causal ? 1 : 0);
         B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     }
@@ -439,26 +455,27 @@ bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
 }
 
 int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
-           float scale, int dtype, cudaStream_t st)
+           float scale, int dtype, cudaStream_t st, bool causal)
 {
+    if (causal && Nq != Nkv) return B200_ERR_UNSUPPORTED;
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
     if ((align & 15) != 0 || !(scale > 0.0f))      // TMA needs 16-byte bases; max(S)*scale needs scale > 0
-        return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st);
+        return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
     if (dtype == B200_DTYPE_BF16) {
         static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
         if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
         if (d == 128) {
             switch (variant) {
-#define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+#define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
                 B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
 #undef B200_V
                 default: return B200_ERR_UNSUPPORTED;
             }
         }
-        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
     }
-    if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
-    return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st);
+    if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
+    return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
 }
 
 }  // namespace b200

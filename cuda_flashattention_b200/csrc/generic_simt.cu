@@ -55,7 +55,7 @@ __device__ __forceinline__ void load_tile(float* dst, const T* src, int valid, i
 template <typename T>
 __global__ void __launch_bounds__(kSimtWarps * 32)
 simt_fwd_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* __restrict__ V, T* __restrict__ O,
-                float* __restrict__ L, float* __restrict__ Mout, int Nq, int Nkv, int d, float scale, int mode)
+                float* __restrict__ L, float* __restrict__ Mout, int Nq, int Nkv, int d, float scale, int mode, int coff)
 {
     extern __shared__ float sm[];
     const int ld = d + 1;
@@ -86,9 +86,11 @@ simt_fwd_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* __res
         float s = 0.0f;
         const float* kr = sK + lane * ld;
         for (int c = 0; c < d; ++c) s = fmaf(q[c], kr[c], s);
-        s = lane < valid ? s * scale : -INFINITY;
+        const bool vis = lane < valid && (t0 + lane) - row <= coff;          // causal: key j visible iff j <= row + coff
+        s = vis ? s * scale : -INFINITY;
         const float m_new = fmaxf(m, warp_max(s));
-        const float p = lane < valid ? expf(s - m_new) : 0.0f;
+        if (m_new == -INFINITY) continue;                                    // whole tile masked, nothing seen yet
+        const float p = vis ? expf(s - m_new) : 0.0f;
         const float alpha = expf(m - m_new);          // m = -inf on the first tile -> 0
         l = alpha * l + warp_sum(p);
         m = m_new;
@@ -141,7 +143,7 @@ template <typename T>
 __global__ void __launch_bounds__(kSimtWarps * 32)
 simt_bwd_dq_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* __restrict__ V, const T* __restrict__ dO,
                    const float* __restrict__ L, const float* __restrict__ D, T* __restrict__ dQ,
-                   int Nq, int Nkv, int d, float scale)
+                   int Nq, int Nkv, int d, float scale, int coff)
 {
     extern __shared__ float sm[];
     const int ld = d + 1;
@@ -178,7 +180,7 @@ simt_bwd_dq_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* __
         const float* kr = sK + lane * ld;
         const float* vr = sV + lane * ld;
         for (int c = 0; c < d; ++c) { s = fmaf(q[c], kr[c], s); dp = fmaf(g[c], vr[c], dp); }
-        const float p = lane < valid ? expf(s * scale - Li) : 0.0f;
+        const float p = (lane < valid && (t0 + lane) - row <= coff) ? expf(s * scale - Li) : 0.0f;
         const float ds = p * (dp - Di);
         for (int j = 0; j < valid; ++j) {
             const float dsj = __shfl_sync(0xffffffffu, ds, j);
@@ -205,7 +207,7 @@ template <typename T>
 __global__ void __launch_bounds__(kSimtWarps * 32)
 simt_bwd_dkv_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* __restrict__ V, const T* __restrict__ dO,
                     const float* __restrict__ L, const float* __restrict__ D, T* __restrict__ dK, T* __restrict__ dV,
-                    int Nq, int Nkv, int d, float scale)
+                    int Nq, int Nkv, int d, float scale, int coff)
 {
     extern __shared__ float sm[];
     const int ld = d + 1;
@@ -245,7 +247,7 @@ simt_bwd_dkv_kernel(const T* __restrict__ Q, const T* __restrict__ K, const T* _
         const float* qi = sQ + lane * ld;
         const float* gi = sG + lane * ld;
         for (int c = 0; c < d; ++c) { s = fmaf(qi[c], kr[c], s); dp = fmaf(gi[c], vr[c], dp); }
-        const float p = lane < valid ? expf(s * scale - sL[lane]) : 0.0f;
+        const float p = (lane < valid && row - (t0 + lane) <= coff) ? expf(s * scale - sL[lane]) : 0.0f;
         const float ds = p * (dp - sD[lane]);
         for (int i2 = 0; i2 < valid; ++i2) {
             const float pi = __shfl_sync(0xffffffffu, p, i2);
@@ -302,26 +304,26 @@ static size_t simt_dkv_smem(int d) { return sizeof(float) * ((size_t)2 * kSimtTi
 
 template <typename T>
 static int simt_fwd_t(const T* Q, const T* K, const T* V, T* O, float* L, float* M, int BH, int Nq, int Nkv, int d,
-                      float scale, int mode, cudaStream_t st)
+                      float scale, int mode, int coff, cudaStream_t st)
 {
     size_t smem = simt_fwd_smem(d);
     if (smem > 48 * 1024) B200_CUDA_TRY(cudaFuncSetAttribute(simt_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((Nq + kSimtWarps - 1) / kSimtWarps, BH);
-    simt_fwd_kernel<T><<<grid, kSimtWarps * 32, smem, st>>>(Q, K, V, O, L, M, Nq, Nkv, d, scale, mode);
+    simt_fwd_kernel<T><<<grid, kSimtWarps * 32, smem, st>>>(Q, K, V, O, L, M, Nq, Nkv, d, scale, mode, coff);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
 }
 
 int simt_fwd(const void* Q, const void* K, const void* V, void* O, float* L, float* M, int BH, int Nq, int Nkv, int d,
-             float scale, int dtype, int mode, cudaStream_t st)
+             float scale, int dtype, int mode, cudaStream_t st, int coff)
 {
     if (d > kSimtMaxD) return B200_ERR_UNSUPPORTED_HEAD_DIM;
     if (BH > 65535) return B200_ERR_INVALID_ARGUMENT;
     if (dtype == B200_DTYPE_F32)
-        return simt_fwd_t((const float*)Q, (const float*)K, (const float*)V, (float*)O, L, M, BH, Nq, Nkv, d, scale, mode, st);
+        return simt_fwd_t((const float*)Q, (const float*)K, (const float*)V, (float*)O, L, M, BH, Nq, Nkv, d, scale, mode, coff, st);
     return simt_fwd_t((const __nv_bfloat16*)Q, (const __nv_bfloat16*)K, (const __nv_bfloat16*)V, (__nv_bfloat16*)O, L, M,
-                      BH, Nq, Nkv, d, scale, mode, st);
+                      BH, Nq, Nkv, d, scale, mode, coff, st);
 }
 
 template <typename T>
@@ -341,20 +343,20 @@ int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtyp
 
 template <typename T>
 static int simt_bwd_t(const T* Q, const T* K, const T* V, const T* dO, const float* L, const float* D, T* dQ, T* dK, T* dV,
-                      int BH, int Nq, int Nkv, int d, float scale, cudaStream_t st)
+                      int BH, int Nq, int Nkv, int d, float scale, int coff, cudaStream_t st)
 {
     size_t s1 = simt_dq_smem(d), s2 = simt_dkv_smem(d);
     if (s1 > 48 * 1024) B200_CUDA_TRY(cudaFuncSetAttribute(simt_bwd_dq_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s1));
     if (s2 > 48 * 1024) B200_CUDA_TRY(cudaFuncSetAttribute(simt_bwd_dkv_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2));
     if (dQ) {
         dim3 g1((Nq + kSimtWarps - 1) / kSimtWarps, BH);
-        simt_bwd_dq_kernel<T><<<g1, kSimtWarps * 32, s1, st>>>(Q, K, V, dO, L, D, dQ, Nq, Nkv, d, scale);
+        simt_bwd_dq_kernel<T><<<g1, kSimtWarps * 32, s1, st>>>(Q, K, V, dO, L, D, dQ, Nq, Nkv, d, scale, coff);
         B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     }
     if (dK && dV) {
         dim3 g2((Nkv + kSimtWarps - 1) / kSimtWarps, BH);
-        simt_bwd_dkv_kernel<T><<<g2, kSimtWarps * 32, s2, st>>>(Q, K, V, dO, L, D, dK, dV, Nq, Nkv, d, scale);
+        simt_bwd_dkv_kernel<T><<<g2, kSimtWarps * 32, s2, st>>>(Q, K, V, dO, L, D, dK, dV, Nq, Nkv, d, scale, coff);
         B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     }
@@ -362,15 +364,15 @@ static int simt_bwd_t(const T* Q, const T* K, const T* V, const T* dO, const flo
 }
 
 int simt_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
-             void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st)
+             void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st, int coff)
 {
     if (d > kSimtMaxD) return B200_ERR_UNSUPPORTED_HEAD_DIM;
     if (BH > 65535) return B200_ERR_INVALID_ARGUMENT;
     if (dtype == B200_DTYPE_F32)
         return simt_bwd_t((const float*)Q, (const float*)K, (const float*)V, (const float*)dO, L, D, (float*)dQ, (float*)dK,
-                          (float*)dV, BH, Nq, Nkv, d, scale, st);
+                          (float*)dV, BH, Nq, Nkv, d, scale, coff, st);
     return simt_bwd_t((const __nv_bfloat16*)Q, (const __nv_bfloat16*)K, (const __nv_bfloat16*)V, (const __nv_bfloat16*)dO, L, D,
-                      (__nv_bfloat16*)dQ, (__nv_bfloat16*)dK, (__nv_bfloat16*)dV, BH, Nq, Nkv, d, scale, st);
+                      (__nv_bfloat16*)dQ, (__nv_bfloat16*)dK, (__nv_bfloat16*)dV, BH, Nq, Nkv, d, scale, coff, st);
 }
 
 int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st)

@@ -105,6 +105,19 @@ B200_API int b200_fa1_fwd_f32(const float* Q, const float* K, const float* V, fl
 B200_API int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L,
                  int B, int H, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t stream);
 
+/* ---- extended entry points (flags) ----------------------------------------------------------------
+ * B200_FLAG_CAUSAL: query row i attends to keys 0 .. i + (Nkv - Nq) only (bottom-right aligned, needs
+ * Nkv >= Nq).  Not in the reference, which is non-causal; its own docs list it as the next step
+ * (src/02_flash_attention_v2_backward/__info__/README.md:173).  Square problems (Nq == Nkv) with
+ * d in {64,128} run on the tensor-core kernels (masked diagonal tiles, tiles above the diagonal are
+ * skipped); other shapes on the generic CUDA-core kernels.  flags = 0 is b200_fa2_fwd / b200_fa2_bwd. */
+#define B200_FLAG_CAUSAL 1
+B200_API int b200_fa2_fwd_ex(const void* Q, const void* K, const void* V, void* O, float* L,
+                    int B, int H, int Nq, int Nkv, int d, float scale, int dtype, int flags, cudaStream_t stream);
+B200_API int b200_fa2_bwd_ex(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                    void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
+                    int flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
 /* ---- host-buffer entry points --------------------------------------------------------------------
  * The reference's drivers own HOST arrays and copy them to the device around every call
  * (src/02_flash_attention_v2_forward/main.cu:42-64, src/02_flash_attention_v2_backward/main.cu:261-289).

@@ -61,12 +61,14 @@ def num_threads():
     return int(lib().oracle_num_threads())
 
 
-def forward(Q, K, V, scale=0.0, want_L=True):
-    """oracle_forward == naive_forward_pass (src/util/naive_attention.h:7-61); Nq may differ from Nkv."""
+def forward(Q, K, V, scale=0.0, want_L=True, causal=False):
+    """oracle_forward == naive_forward_pass (src/util/naive_attention.h:7-61); Nq may differ from Nkv.
+    causal=True is an extension (the reference is non-causal): row i sees keys 0 .. i + (Nkv - Nq)."""
     Q, q = _f(Q); K, k = _f(K); V, v = _f(V)
     Nq, d = Q.shape; Nkv = K.shape[0]
     O = np.empty((Nq, d), np.float32); L = np.empty((Nq,), np.float32)
-    lib().oracle_forward(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp) if want_L else None,
+    fn = lib().oracle_forward_causal if causal else lib().oracle_forward
+    fn(q, k, v, O.ctypes.data_as(_fp), L.ctypes.data_as(_fp) if want_L else None,
                          C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
     return (O, L) if want_L else O
 
@@ -128,12 +130,13 @@ def backward_jacobian(Q, K, V, dO, scale):
     return dQ, dK, dV
 
 
-def backward(Q, K, V, dO, scale=0.0):
-    """O(N^2 d) restatement (dS = P o (dP - D)), double accumulation; Nq may differ from Nkv."""
+def backward(Q, K, V, dO, scale=0.0, causal=False):
+    """O(N^2 d) restatement (dS = P o (dP - D)), double accumulation; Nq may differ from Nkv.  causal: see forward."""
     Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
     Nq, d = Q.shape; Nkv = K.shape[0]
     dQ = np.empty((Nq, d), np.float32); dK = np.empty((Nkv, d), np.float32); dV = np.empty((Nkv, d), np.float32)
-    lib().oracle_backward(q, k, v, g, dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp), dV.ctypes.data_as(_fp),
+    fn = lib().oracle_backward_causal if causal else lib().oracle_backward
+    fn(q, k, v, g, dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp), dV.ctypes.data_as(_fp),
                           C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
     return dQ, dK, dV
 

@@ -1,7 +1,7 @@
 // kbench.cu -- native micro-harness for the C-ABI (no Python/torch start-up): device-resident
 // N(0,1) inputs, CUDA-event timing of b200_fa2_fwd / b200_fa2_bwd, optional in-kernel trace dump
 // (library built with EXTRA=-DB200_TRACE).  Not the contract bench (that is bench.py).
-//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace]
+//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal]
 //   env B200ATTN_LIB = path of the shared object (default: cuda_flashattention_b200/libb200attn.so)
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
@@ -35,6 +35,9 @@ __global__ void fill_normal(T* p, size_t n, uint64_t seed, float sigma) {
 typedef int (*fwd_t)(const void*, const void*, const void*, void*, float*, int, int, int, int, int, float, int, cudaStream_t);
 typedef int (*bwd_t)(const void*, const void*, const void*, const void*, const float*, const void*, void*, void*, void*,
                      int, int, int, int, int, float, int, void*, size_t, cudaStream_t);
+typedef int (*fwdx_t)(const void*, const void*, const void*, void*, float*, int, int, int, int, int, float, int, int, cudaStream_t);
+typedef int (*bwdx_t)(const void*, const void*, const void*, const void*, const float*, const void*, void*, void*, void*,
+                      int, int, int, int, int, float, int, int, void*, size_t, cudaStream_t);
 typedef size_t (*ws_t)(int, int, int, int, int, int);
 typedef int (*trace_t)(long long*, int);
 
@@ -44,17 +47,21 @@ int main(int argc, char** argv)
     const char* mode = argv[1];
     const int B = atoi(argv[2]), H = atoi(argv[3]), N = atoi(argv[4]), d = atoi(argv[5]);
     const bool f32 = strcmp(argv[6], "f32") == 0;
-    int iters = 10; bool trace = false;
-    for (int i = 7; i < argc; ++i) { if (!strcmp(argv[i], "--trace")) trace = true; else iters = atoi(argv[i]); }
+    int iters = 10; bool trace = false, causal = false;
+    for (int i = 7; i < argc; ++i) {
+        if (!strcmp(argv[i], "--trace")) trace = true; else if (!strcmp(argv[i], "--causal")) causal = true; else iters = atoi(argv[i]);
+    }
     const char* path = getenv("B200ATTN_LIB");
     if (!path) path = "cuda_flashattention_b200/libb200attn.so";
     void* h = dlopen(path, RTLD_NOW);
     if (!h) { fprintf(stderr, "dlopen %s: %s\n", path, dlerror()); return 2; }
     fwd_t fwd = (fwd_t)dlsym(h, "b200_fa2_fwd");
     bwd_t bwd = (bwd_t)dlsym(h, "b200_fa2_bwd");
+    fwdx_t fwdx = (fwdx_t)dlsym(h, "b200_fa2_fwd_ex");
+    bwdx_t bwdx = (bwdx_t)dlsym(h, "b200_fa2_bwd_ex");
     ws_t wsb = (ws_t)dlsym(h, "b200_fa2_bwd_workspace_bytes");
     trace_t tr = (trace_t)dlsym(h, strcmp(mode, "bwd") == 0 ? "b200_debug_trace_read_bwd" : "b200_debug_trace_read");
-    if (!fwd || !bwd || !wsb) { fprintf(stderr, "missing symbols\n"); return 2; }
+    if (!fwd || !bwd || !wsb || !fwdx || !bwdx) { fprintf(stderr, "missing symbols\n"); return 2; }
 
     const size_t n = (size_t)B * H * N * d, eb = f32 ? 4 : 2;
     void *Q, *K, *V, *O, *dO, *dQ, *dK, *dV, *ws; float* L;
@@ -71,8 +78,9 @@ int main(int argc, char** argv)
     }
     CK(cudaDeviceSynchronize());
     const bool do_f = strcmp(mode, "bwd") != 0, do_b = strcmp(mode, "fwd") != 0;
-    auto run_f = [&]() { int s = fwd(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 0); if (s) { fprintf(stderr, "fwd status %d\n", s); exit(3); } };
-    auto run_b = [&]() { int s = bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, ws, wsn, 0); if (s) { fprintf(stderr, "bwd status %d\n", s); exit(3); } };
+    auto run_f = [&]() { int s = causal ? fwdx(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 1, 0) : fwd(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 0); if (s) { fprintf(stderr, "fwd status %d\n", s); exit(3); } };
+    auto run_b = [&]() { int s = causal ? bwdx(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, 1, ws, wsn, 0)
+                                          : bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, ws, wsn, 0); if (s) { fprintf(stderr, "bwd status %d\n", s); exit(3); } };
     run_f();
     for (int i = 0; i < 3; ++i) { if (do_f) run_f(); if (do_b) run_b(); }
     CK(cudaDeviceSynchronize());
@@ -92,8 +100,10 @@ int main(int argc, char** argv)
     }
     auto med = [](std::vector<float> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
     auto mn = [](std::vector<float> v) { return *std::min_element(v.begin(), v.end()); };
-    const double ff = 4.0 * B * H * (double)N * N * d, fb = 10.0 * B * H * (double)N * N * d;
-    printf("B=%d H=%d N=%d d=%d %s:", B, H, N, d, f32 ? "f32" : "bf16");
+    // causal: the visible half of the score matrix only (N (N + 1) / 2 pairs)
+    const double pairs = causal ? 0.5 * N * ((double)N + 1) : (double)N * N;
+    const double ff = 4.0 * B * H * pairs * d, fb = 10.0 * B * H * pairs * d;
+    printf("B=%d H=%d N=%d d=%d %s%s:", B, H, N, d, f32 ? "f32" : "bf16", causal ? " causal" : "");
     if (do_f) printf("  fwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tf), ff / med(tf) / 1e9, mn(tf), ff / mn(tf) / 1e9);
     if (do_b) printf("  bwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tb), fb / med(tb) / 1e9, mn(tb), fb / mn(tb) / 1e9);
     printf("\n");
