@@ -21,6 +21,10 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# The ring path runs four streams with long stream-memop waits beside NCCL's and torch's own; with the default 8
+# hardware queues two of them can share one and a wait then stalls the attention launches queued behind it
+# (profiles/README.md, r1c).  Has to be set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "attention TFLOP/s (FA2 fwd+bwd, algorithmic 14*B*H*N^2*d), whole job"
 UNIT = "TFLOP/s"

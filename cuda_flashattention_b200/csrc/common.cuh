@@ -41,6 +41,9 @@ int simt_bwd(const void* Q, const void* K, const void* V, const void* dO, const 
              void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st,
              int coff = kNoCausal);
 int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st);
+// (O, L) = merge of n partials at Op + s * o_stride (elements) / Lp + s * l_stride, plus (O, L) itself when `running`
+int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o_stride, size_t l_stride, int n, bool running,
+                    size_t rows, int d, int dtype, cudaStream_t st);
 
 // ---- tcgen05 tensor-core kernels (fwd_sm100.cu / bwd_sm100.cu) ------------------------------------
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv);

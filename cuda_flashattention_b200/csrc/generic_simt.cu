@@ -297,6 +297,58 @@ lse_merge_kernel(T* __restrict__ Oa, float* __restrict__ La, const T* __restrict
     if (lane == 0) La[row] = lnew;
 }
 
+// ---------------------------------------------------------------------------------------------
+// n-way merge (ring forward, deferred): partial s lives at Op + s * o_stride elements / Lp + s * l_stride;
+// with `running` the current (O, L) is one more input.  L = log sum_s e^(L_s), O = sum_s e^(L_s - L) O_s,
+// accumulated in fp32 and rounded once.  One warp per row, 4 elements per lane and trip; HBM-bound.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+lse_merge_multi_kernel(T* __restrict__ O, float* __restrict__ L, const T* __restrict__ Op, const float* __restrict__ Lp,
+                       size_t o_stride, size_t l_stride, int n, int running, size_t rows, int d)
+{
+    const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    float mx = running ? L[row] : -INFINITY;
+    for (int s = 0; s < n; ++s) mx = fmaxf(mx, Lp[s * l_stride + row]);
+    float tot = 0.f;
+    if (mx != -INFINITY) {
+        if (running) tot += expf(L[row] - mx);
+        for (int s = 0; s < n; ++s) tot += expf(Lp[s * l_stride + row] - mx);
+    }
+    const float inv = tot > 0.f ? 1.0f / tot : 0.f;
+    for (int c = lane * 4; c < d; c += 128) {
+        const int w = min(4, d - c);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        if (running) {
+            const float wr = mx == -INFINITY ? 0.f : expf(L[row] - mx) * inv;
+            for (int e = 0; e < w; ++e) acc[e] = wr * ldf(O + row * d + c + e);
+        }
+        for (int s = 0; s < n; ++s) {
+            const float ws = mx == -INFINITY ? 0.f : expf(Lp[s * l_stride + row] - mx) * inv;
+            const T* src = Op + s * o_stride + row * d + c;
+            if (w == 4 && (d & 3) == 0) {
+                if constexpr (sizeof(T) == 2) {
+                    const uint2 v = *reinterpret_cast<const uint2*>(src);
+                    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&v.x), b = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+                    acc[0] = fmaf(ws, __low2float(a), acc[0]); acc[1] = fmaf(ws, __high2float(a), acc[1]);
+                    acc[2] = fmaf(ws, __low2float(b), acc[2]); acc[3] = fmaf(ws, __high2float(b), acc[3]);
+                } else {
+                    const float4 v = *reinterpret_cast<const float4*>(src);
+                    acc[0] = fmaf(ws, v.x, acc[0]); acc[1] = fmaf(ws, v.y, acc[1]);
+                    acc[2] = fmaf(ws, v.z, acc[2]); acc[3] = fmaf(ws, v.w, acc[3]);
+                }
+            } else {
+                for (int e = 0; e < w; ++e) acc[e] = fmaf(ws, ldf(src + e), acc[e]);
+            }
+        }
+        for (int e = 0; e < w; ++e) stf(O + row * d + c + e, acc[e]);
+    }
+    __syncwarp();
+    if (lane == 0) L[row] = mx == -INFINITY ? -INFINITY : mx + logf(tot);
+}
+
 // ------------------------------------------------------------------------------------ launchers
 static size_t simt_fwd_smem(int d) { return sizeof(float) * ((size_t)2 * kSimtTile * (d + 1) + (size_t)kSimtWarps * d); }
 static size_t simt_dq_smem(int d) { return sizeof(float) * ((size_t)2 * kSimtTile * (d + 1) + (size_t)2 * kSimtWarps * d); }
@@ -381,6 +433,21 @@ int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows,
     unsigned grid = (unsigned)((rows + 7) / 8);
     if (dtype == B200_DTYPE_F32) lse_merge_kernel<float><<<grid, 256, 0, st>>>((float*)Oa, La, (const float*)Ob, Lb, rows, d);
     else lse_merge_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)Oa, La, (const __nv_bfloat16*)Ob, Lb, rows, d);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
+int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o_stride, size_t l_stride, int n, bool running,
+                    size_t rows, int d, int dtype, cudaStream_t st)
+{
+    if (rows == 0 || (n == 0 && running)) return B200_OK;
+    unsigned grid = (unsigned)((rows + 7) / 8);
+    if (dtype == B200_DTYPE_F32)
+        lse_merge_multi_kernel<float><<<grid, 256, 0, st>>>((float*)O, L, (const float*)Op, Lp, o_stride, l_stride, n, running ? 1 : 0, rows, d);
+    else
+        lse_merge_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)O, L, (const __nv_bfloat16*)Op, Lp, o_stride, l_stride, n,
+                                                                     running ? 1 : 0, rows, d);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;

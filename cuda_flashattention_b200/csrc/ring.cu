@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include <nccl.h>
 #include <cuda.h>
+#include <algorithm>
 #include <mutex>
 #include <math.h>
 #include <stdlib.h>
@@ -368,8 +369,13 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t kv_bytes = (size_t)B * H * Nl * d * es;
     const size_t l_bytes = (size_t)B * H * Nl * sizeof(float);
-    // scratch: 2 x (K,V) receive buffers + 2 x (partial O + partial LSE)
-    const size_t total = 4 * align256(kv_bytes) + 2 * (align256(kv_bytes) + align256(l_bytes));
+    // scratch: 2 x (K,V) receive buffers + NB x (partial O + partial LSE).  One partial per ring step when that fits
+    // in 4 GB (it does for every shape in BASELINE.json): no step then waits for a merge -- they are all folded by one
+    // n-way merge at the end -- and each attention kernel can start in the tail of the previous one.
+    const size_t part_bytes = align256(kv_bytes) + align256(l_bytes);
+    int NB = (int)std::min<size_t>((size_t)nranks, std::max<size_t>(2, ((size_t)4 << 30) / part_bytes));
+    if (const char* e = getenv("B200_RING_MAX_PARTIALS")) NB = std::max(2, std::min(NB, atoi(e)));   // test hook (same on all ranks)
+    const size_t total = 4 * align256(kv_bytes) + (size_t)NB * part_bytes;
     void* base;
     bool ce = false;
     B200_TRY(link_prepare(rs, comm, rank, nranks, total, &base, &ce));
@@ -382,11 +388,12 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
         offK[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Kb[i] = p; p += align256(kv_bytes);
         offV[i] = (size_t)(p - reinterpret_cast<uint8_t*>(base)); Vb[i] = p; p += align256(kv_bytes);
     }
-    void* Opb[2]; float* Lpb[2];
-    for (int i = 0; i < 2; ++i) {
-        Opb[i] = p; p += align256(kv_bytes);
-        Lpb[i] = reinterpret_cast<float*>(p); p += align256(l_bytes);
-    }
+    // partial s: O at Opart + s * part_bytes, LSE right behind it
+    uint8_t* Opart = p;
+    float* Lpart = reinterpret_cast<float*>(p + align256(kv_bytes));
+    auto Opb = [&](int i) { return (void*)(Opart + (size_t)i * part_bytes); };
+    auto Lpb = [&](int i) { return reinterpret_cast<float*>(Opart + (size_t)i * part_bytes + align256(kv_bytes)); };
+    if (!ce) NB = 2;
 
     const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
     // the side streams may start once everything already enqueued on the caller's stream is done
@@ -404,7 +411,8 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
         // copy-engine mode: the attention of consecutive steps runs on two alternating streams (the merges stay
         // on the caller's stream), so a step's last, partly filled wave overlaps the next step's first one
         cudaStream_t as = ce ? rs->attn_stream[step & 1] : st;
-        void* Op = Opb[step & 1]; float* Lp = Lpb[step & 1];
+        const int pb = ce ? step % NB : (step & 1);
+        void* Op = Opb(pb); float* Lp = Lpb(pb);
         if (ce && step >= 1) {
             // the block of this step was pushed into cur_slot by the previous rank: both streams wait for it
             const uint32_t k = ++lk.in_kv[cur_slot];
@@ -425,16 +433,22 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
             }
         }
         // attention of the local queries against the current block (overlaps the exchange above)
-        if (ce && step >= 3) B200_CUDA_TRY(cudaStreamWaitEvent(as, rs->ev_merge[step & 1], 0));   // merge(step-2) has consumed this partial buffer
-        if (step == 0) B200_TRY(b200_fa2_fwd(Q, Kc, Vc, O, L, B, H, Nl, Nl, d, scale, dtype, as));
-        else B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
         if (ce) {
+            // (only when the partials did not all fit) the group merge that consumed this buffer must be done
+            if (step >= NB) B200_CUDA_TRY(cudaStreamWaitEvent(as, rs->ev_merge[0], 0));
+            B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
             B200_CUDA_TRY(cudaEventRecord(rs->ev_attn[step & 1], as));
             B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_attn[step & 1], 0));
-        }
-        if (step >= 1) {
-            B200_TRY(b200_lse_merge(O, L, Op, Lp, B, H, Nl, d, dtype, st));
-            if (ce) B200_CUDA_TRY(cudaEventRecord(rs->ev_merge[step & 1], st));           // partial buffer (step & 1) is free again
+            if (pb == NB - 1 || step == nranks - 1) {
+                // fold partials 0 .. pb (and, after the first group, the running result) into (O, L)
+                B200_TRY(lse_merge_multi(O, L, Opart, Lpart, part_bytes / es, part_bytes / sizeof(float), pb + 1, step >= NB,
+                                         (size_t)B * H * Nl, d, dtype, st));
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_merge[0], st));
+            }
+        } else {
+            if (step == 0) B200_TRY(b200_fa2_fwd(Q, Kc, Vc, O, L, B, H, Nl, Nl, d, scale, dtype, as));
+            else B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
+            if (step >= 1) B200_TRY(b200_lse_merge(O, L, Op, Lp, B, H, Nl, d, dtype, st));
         }
         if (ce) {
             if (step >= 1) {
