@@ -155,6 +155,7 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
 // dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> registers -> fp32 red.global.add straight
 // into the dQ accumulator.  A warp's 32 lanes hold 32 consecutive d of one q row, so every red
 // instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
+template <int DR>
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
                                                float* __restrict__ dQacc, int Nq, int n_it, int qt_min, int i_off, int bh,
                                                int dbg)
@@ -178,15 +179,15 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         __syncwarp();
         if (lane0) mbar_arrive(bar_dQ_empty);                          // TMEM columns are free again
         B200_TRB(1, i, 1);
-        float* dst = dQacc + ((size_t)bh * Nq + (size_t)qt * BM) * D + r;
+        float* dst = dQacc + ((size_t)bh * Nq + (size_t)qt * BM) * DR + r;
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
-        if (!(dbg & 1)) {
+        if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
             if (q_valid == BM) {
 #pragma unroll
-                for (int q = 0; q < BM; ++q) red_add_f32(dst + q * D, __uint_as_float(v[q]));
+                for (int q = 0; q < BM; ++q) red_add_f32(dst + q * DR, __uint_as_float(v[q]));
             } else {
 #pragma unroll
-                for (int q = 0; q < BM; ++q) if (q < q_valid) red_add_f32(dst + q * D, __uint_as_float(v[q]));
+                for (int q = 0; q < BM; ++q) if (q < q_valid) red_add_f32(dst + q * DR, __uint_as_float(v[q]));
             }
         }
         B200_TRB(1, i, 2);
@@ -194,6 +195,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
 }
 
 // dV (w = 0) / dK (w = 1) epilogue: TMEM fp32 [128 kv x 128 d] -> bf16 -> swizzled smem -> TMA store.
+template <int DR>
 __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem, const CUtensorMap* tm, int kv0, int bh)
 {
     using namespace bwd;
@@ -201,7 +203,7 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
     const uint32_t tA = tmem + (w == 0 ? TM_DV : TM_DK) + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
     uint8_t* out = smem + (w == 0 ? OFF_V : OFF_K);                    // K / V tiles are dead after the last MMA
 #pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
+    for (int c = 0; c < DR / 32; ++c) {
         uint32_t o[32];
         B200_TMEM_LD_32(tA + 32 * c, o);
         tmem_wait_ld();
@@ -220,12 +222,16 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
     named_bar_sync(4 + w, 128);
     if (r == 0) {
         tma_store_3d(tm, out, 0, kv0, bh);
-        tma_store_3d(tm, out + KV_BOX, 64, kv0, bh);
+        if (DR == 128) tma_store_3d(tm, out + KV_BOX, 64, kv0, bh);
         tma_store_commit();
         tma_store_wait<0>();
     }
 }
 
+// DR = real head dimension (128 or 64).  The tile layout is the d = 128 one; for d = 64 only the first 64-wide box of
+// every tile is loaded and the MMAs run over 64 (M1, M2: K extent; M3, M4: N extent).  M5 has d as its M extent, which
+// stays 128: the second box of K is zero-filled once, so lanes 64..127 of dQ^T are zero and are not drained.
+template <int DR>
 __global__ void __launch_bounds__(bwd::THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -272,16 +278,22 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         tma_prefetch_desc(&tmdK); tma_prefetch_desc(&tmdV);
     }
     if (warp == 2) { tmem_alloc<512>(tmem_slot); tmem_relinquish(); }
+    if (DR == 64) {
+        for (int i = threadIdx.x; i < KV_BOX / 16; i += THREADS)
+            reinterpret_cast<uint4*>(smem + OFF_K + KV_BOX)[i] = make_uint4(0u, 0u, 0u, 0u);
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    constexpr int NBOX = DR / 64;
 
     if (warp == 0) {
         // ================================ TMA producer ================================
         if (elect_one()) {
-            mbar_expect_tx(bar_KV, 2 * KV_TILE);
-            for (int b = 0; b < 2; ++b) {
+            mbar_expect_tx(bar_KV, 2 * NBOX * KV_BOX);
+            for (int b = 0; b < NBOX; ++b) {
                 tma_load_3d(smem + OFF_K + b * KV_BOX, &tmK, bar_KV, b * 64, kv0, bh, kEvictFirst);
                 tma_load_3d(smem + OFF_V + b * KV_BOX, &tmV, bar_KV, b * 64, kv0, bh, kEvictFirst);
             }
@@ -293,8 +305,8 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 if (qt >= n_it) qt -= n_it;
                 qt += qt_min;
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
-                mbar_expect_tx(&bar_in_full[s], 2 * Q_TILE + 2 * STAT_BYTES);
-                for (int b = 0; b < 2; ++b) {
+                mbar_expect_tx(&bar_in_full[s], 2 * NBOX * Q_BOX + 2 * STAT_BYTES);
+                for (int b = 0; b < NBOX; ++b) {
                     tma_load_3d(smem + OFF_Q + s * Q_TILE + b * Q_BOX, &tmQ, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
                     tma_load_3d(smem + OFF_DO + s * Q_TILE + b * Q_BOX, &tmdO, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
                 }
@@ -306,13 +318,13 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         // ================================ MMA issuer ==================================
         if (elect_one()) {
             constexpr uint32_t idesc_ss = make_idesc(kFmtBF16, 128, BM, false, false);   // M1, M2
-            constexpr uint32_t idesc_ts = make_idesc(kFmtBF16, 128, D, false, true);     // M3, M4
+            constexpr uint32_t idesc_ts = make_idesc(kFmtBF16, 128, DR, false, true);    // M3, M4
             constexpr uint32_t idesc_dq = make_idesc(kFmtBF16, 128, BM, true, true);     // M5
             const uint32_t sb = smem_u32(smem);
             auto mma_ss = [&](uint32_t a_tile, uint32_t b_tile, uint32_t d_col) {        // D = A[128 x d] B[64 x d]^T
                 const uint64_t ad = make_sdesc(a_tile, 16, 1024, 2), bd = make_sdesc(b_tile, 16, 1024, 2);
 #pragma unroll
-                for (int kk = 0; kk < D / 16; ++kk)
+                for (int kk = 0; kk < DR / 16; ++kk)
                     umma_f16_ss(tmem + d_col, sdesc_advance(ad, (kk >> 2) * KV_BOX + (kk & 3) * 32),
                                 sdesc_advance(bd, (kk >> 2) * Q_BOX + (kk & 3) * 32), idesc_ss, kk > 0);
             };
@@ -370,9 +382,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_it, qt_min, i_off, kv0, causal, scale_log2, scale);
         mbar_wait(bar_done, 0);
         tc_fence_after();
-        bwd_epilogue(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
+        bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
     } else if (warp >= 12) {
-        bwd_drain_role(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_it, qt_min, i_off, bh, dbg);
+        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_it, qt_min, i_off, bh, dbg);
     }
 
     tc_fence_before();
@@ -422,7 +434,7 @@ static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv)
 {
-    return dtype == B200_DTYPE_BF16 && d == 128 && Nq >= 1 && Nkv >= 1;
+    return dtype == B200_DTYPE_BF16 && (d == 128 || d == 64) && Nq >= 1 && Nkv >= 1;
 }
 
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
@@ -432,6 +444,7 @@ size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
     return 2 * al256((size_t)BH * Nq_pad * sizeof(float)) + al256((size_t)BH * Nq * d * sizeof(float));
 }
 
+template <int DR>
 static int bwd_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
                       float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st,
                       bool causal = false)
@@ -439,20 +452,20 @@ static int bwd_launch(const void* Q, const void* K, const void* V, const void* d
     using namespace bwd;
     static bool attr_set = false;
     if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         attr_set = true;
     }
     const int Nq_pad = (Nq + 63) / 64 * 64;
     CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
     const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, D, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, D, BM, 64) ||
-        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, D, BN, 64) ||
-        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, D, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, D, BN, 64))
+    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, DR, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, DR, BM, 64) ||
+        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, DR, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, DR, BN, 64) ||
+        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, DR, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, DR, BN, 64))
         return B200_ERR_CUDA;
     dim3 grid((Nkv + BN - 1) / BN, BH);
     static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
     if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
-    bwd_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
+    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
                                             scale * 1.4426950408889634f, scale, dbg, causal ? 1 : 0);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
@@ -474,14 +487,15 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
     float* L2p = reinterpret_cast<float*>(p); p += al256((size_t)BH * Nq_pad * sizeof(float));
     float* Dp = reinterpret_cast<float*>(p);  p += al256((size_t)BH * Nq_pad * sizeof(float));
     float* dQacc = reinterpret_cast<float*>(p);
-    const size_t n_dq = (size_t)BH * Nq * D;
+    const size_t n_dq = (size_t)BH * Nq * d;
 
     const size_t total = (size_t)BH * Nq_pad;
     pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
-    B200_TRY(bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
+    if (d == 128) B200_TRY(bwd_launch<128>(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
+    else B200_TRY(bwd_launch<64>(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
     unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
     if (cgrid > 148u * 8) cgrid = 148u * 8;
     cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);
@@ -520,7 +534,7 @@ int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO
     const int Nq_pad = (Nq + 63) / 64 * 64;
     const float* L2p = reinterpret_cast<const float*>(stats);
     const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
-    return bwd_launch(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, scale, st);
+    return bwd_launch<128>(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, scale, st);
 }
 
 }  // namespace b200

@@ -41,6 +41,16 @@ def test_bwd_square(N):
     _check(N, N, 128, N)
 
 
+@pytest.mark.parametrize("N", [64, 200, 1024, 2048])
+def test_bwd_square_d64(N):
+    # d = 64 runs the same kernel on half-width tiles (only dQ^T = K^T dS keeps the 128-row MMA, zero padded)
+    _check(N, N, 64, 3 * N)
+
+
+def test_bwd_d64_cross_lengths_batched():
+    _check(333, 200, 64, 6, B=2, H=2)
+
+
 def test_bwd_cross_lengths_batched():
     _check(200, 333, 128, 5, B=2, H=3)
 

@@ -66,9 +66,9 @@ def test_causal_needs_nq_le_nkv():
         fa.flash_attention_2_forward(q, k, k, 0.0, causal=True)
 
 
-@pytest.mark.parametrize("N,B,H", [(64, 1, 1), (128, 1, 1), (192, 1, 1), (256, 1, 1), (1000, 1, 1), (2048, 1, 1), (640, 2, 3)])
-def test_causal_backward_tensor_core(N, B, H):
-    d = 128
+@pytest.mark.parametrize("N,B,H,d", [(64, 1, 1, 128), (128, 1, 1, 128), (192, 1, 1, 128), (256, 1, 1, 128), (1000, 1, 1, 128),
+                                     (2048, 1, 1, 128), (640, 2, 3, 128), (1000, 1, 2, 64)])
+def test_causal_backward_tensor_core(N, B, H, d):
     rng = np.random.default_rng(77 + N)
     q, k, v, do = [_rand((B, H, N, d), rng, torch.bfloat16) for _ in range(4)]
     assert fa.uses_tensor_cores(torch.bfloat16, d, N, N, backward=True)
