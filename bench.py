@@ -31,8 +31,13 @@ UNIT = "TFLOP/s"
 B0, H0, N0, D0 = 8, 16, 8192, 128
 
 
+WORKLOAD = "default"          # --workload c5: BASELINE.json configs[4] (B=1 H=32 N=262144 d=128) sharded over the ranks
+
+
 def workload(n_gpus):
     """(B, H, N_local, N_total, d) per the weak-scaling series described above."""
+    if WORKLOAD == "c5":
+        return 1, 32, 262144 // n_gpus, 262144, D0
     bh = (B0 * H0) // n_gpus
     H = H0
     B = max(1, bh // H)
@@ -43,6 +48,10 @@ def workload(n_gpus):
 
 def config_dict(n_gpus):
     B, H, Nl, Nt, d = workload(n_gpus)
+    if WORKLOAD == "c5":
+        return {"workload": f"C5 long-context ring fwd+bwd B=1 H=32 N=262144 d=128 bf16 over {n_gpus} GPUs (N_local={Nl})",
+                "B": B, "H": H, "N_total": Nt, "N_local": Nl, "d": d, "parallelism": f"ring-sp{n_gpus}",
+                "l2_policy": "inputs larger than L2"}
     name = ("C3 FA2 fwd+bwd B=8 H=16 N=8192 d=128 bf16" if n_gpus == 1 else
             f"ring fwd+bwd B={B} H={H} N={Nt} d={d} bf16 over {n_gpus} GPUs (N_local={Nl}; C4 shape at 8 GPUs)")
     return {"workload": name, "B": B, "H": H, "N_total": Nt, "N_local": Nl, "d": d,
@@ -344,8 +353,11 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="default", choices=["default", "c5"],
+                    help="c5 = the long-context ring config (not the driver's headline line)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
+    globals()["WORKLOAD"] = args.workload
     if args.impl == "reference":
         run_reference(args)
     else:
