@@ -6,5 +6,6 @@ Importing this package loads libb200attn.so; it raises if the library was not bu
 from ._lib import lib, LIB_PATH, EXPORTS, B200Error, B200_DTYPE_BF16, B200_DTYPE_F32  # noqa: F401
 from .attention import (flash_attention_2_forward, flash_attention_2_backward, flash_attention,  # noqa: F401
                         lse_merge_, uses_tensor_cores, flash_attention_2_forward_host,
-                        flash_attention_2_forward_backward_host)
+                        flash_attention_2_forward_backward_host, attention_forward, attention_backward,
+                        flash_attn_func)
 from .ring import RingComm, ring_attention_forward, ring_attention_backward, ring_kv_block  # noqa: F401

@@ -22,6 +22,23 @@ lib = C.CDLL(LIB_PATH)
 
 _vp, _fp, _i, _f, _sz = C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_size_t
 
+
+
+class Layout(C.Structure):
+    """b200_layout: batch / head / row strides in elements (all zero = contiguous [B,H,N,d])."""
+    _fields_ = [("batch_stride", C.c_longlong), ("head_stride", C.c_longlong), ("row_stride", C.c_longlong)]
+
+
+class AttnDesc(C.Structure):
+    """b200_attn_desc (include/b200attn.h)."""
+    _fields_ = [("B", _i), ("H", _i), ("Hkv", _i), ("Nq", _i), ("Nkv", _i), ("d", _i), ("dtype", _i), ("flags", _i),
+                ("scale", _f),
+                ("q", Layout), ("k", Layout), ("v", Layout), ("o", Layout), ("d_o", Layout), ("dq", Layout), ("dk", Layout),
+                ("dv", Layout)]
+
+
+_dp = C.POINTER(AttnDesc)
+
 _SIGS = {
     "b200_strerror": (C.c_char_p, [_i]),
     "b200_last_cuda_error": (_i, []),
@@ -36,6 +53,8 @@ _SIGS = {
     "b200_fa2_fwd": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_fwd_ex": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _i, _f, _i, _i, _vp]),
     "b200_fa2_bwd_ex": (_i, [_vp] * 9 + [_i, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
+    "b200_fa2_fwd_desc": (_i, [_dp, _vp, _vp, _vp, _vp, _fp, _vp]),
+    "b200_fa2_bwd_desc": (_i, [_dp] + [_vp] * 9 + [_vp, _sz, _vp]),
     "b200_fa2_fwd_host": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),

@@ -15,7 +15,7 @@ Tensors are [N, d] (one head, the reference's shape) or [B, H, N, d]; fp32 or bf
 """
 import torch
 
-from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32
+from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32, AttnDesc, Layout
 
 FLAG_CAUSAL = 1  # B200_FLAG_CAUSAL (include/b200attn.h)
 
@@ -153,3 +153,87 @@ def flash_attention_2_forward_backward_host(Q, K, V, dO, softmax_scale=0.0, out=
                                         dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), B, H, N, d, float(softmax_scale),
                                         _dtype_code(Q), _stream()), "b200_fa2_fwd_bwd_host")
     return O, L, dQ, dK, dV
+
+
+# ---------------------------------------------------------------------------------------------------
+# The callers' side of the boundary: strided [B,H,N,d] / token-major [B,N,H,d] tensors,
+# grouped K/V heads (GQA / MQA) and an autograd function, all through b200_fa2_fwd_desc / _bwd_desc.
+# The reference stops at contiguous single-head slabs (__info__/README.md:175).
+# ---------------------------------------------------------------------------------------------------
+def _dims(t, layout):
+    """(B, H, N, d, Layout) of a 4-D tensor whose last dimension is contiguous."""
+    if t.dim() != 4 or t.stride(-1) != 1:
+        raise ValueError("expected a 4-D tensor with a contiguous last dimension")
+    if layout == "bhnd":
+        B, H, N, d = t.shape
+        return B, H, N, d, Layout(t.stride(0), t.stride(1), t.stride(2))
+    if layout == "bnhd":
+        B, N, H, d = t.shape
+        return B, H, N, d, Layout(t.stride(0), t.stride(2), t.stride(1))
+    raise ValueError("layout must be 'bhnd' or 'bnhd'")
+
+
+def _make_desc(q, k, v, layout, causal, softmax_scale):
+    for t in (q, k, v):
+        if not t.is_cuda:
+            raise ValueError("cuda_flashattention_b200 has no CPU path: tensors must live on a CUDA device")
+    if not (q.dtype == k.dtype == v.dtype) or not (q.device == k.device == v.device):
+        raise ValueError("q, k, v must share device and dtype")
+    B, H, Nq, d, lq = _dims(q, layout)
+    Bk, Hkv, Nkv, dk, lk = _dims(k, layout)
+    Bv, Hv, Nv, dv, lv = _dims(v, layout)
+    if (Bk, dk) != (B, d) or (Bv, Hv, Nv, dv) != (Bk, Hkv, Nkv, dk) or Hkv < 1 or H % Hkv != 0:
+        raise ValueError("q/k/v shape mismatch (K/V heads must divide the query heads)")
+    desc = AttnDesc(B=B, H=H, Hkv=Hkv, Nq=Nq, Nkv=Nkv, d=d, dtype=_dtype_code(q), flags=FLAG_CAUSAL if causal else 0,
+                    scale=float(softmax_scale or 0.0), q=lq, k=lk, v=lv)
+    return desc, (B, H, Nq)
+
+
+def attention_forward(q, k, v, causal=False, softmax_scale=None, layout="bhnd"):
+    """O (same dimension order as q, contiguous) and L [B,H,Nq] for strided / grouped-head inputs."""
+    desc, (B, H, Nq) = _make_desc(q, k, v, layout, causal, softmax_scale)
+    O = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+    L = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
+    desc.o = _dims(O, layout)[4]
+    with torch.cuda.device(q.device):
+        check(lib.b200_fa2_fwd_desc(desc, q.data_ptr(), k.data_ptr(), v.data_ptr(), O.data_ptr(), L.data_ptr(), _stream()),
+              "b200_fa2_fwd_desc")
+    return O, L
+
+
+def attention_backward(q, k, v, O, L, dO, causal=False, softmax_scale=None, layout="bhnd"):
+    desc, _ = _make_desc(q, k, v, layout, causal, softmax_scale)
+    if dO.stride(-1) != 1:
+        dO = dO.contiguous()
+    dQ = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+    dK = torch.empty(k.shape, dtype=k.dtype, device=k.device)
+    dV = torch.empty(v.shape, dtype=v.dtype, device=v.device)
+    desc.o, desc.d_o = _dims(O, layout)[4], _dims(dO, layout)[4]
+    desc.dq, desc.dk, desc.dv = _dims(dQ, layout)[4], _dims(dK, layout)[4], _dims(dV, layout)[4]
+    with torch.cuda.device(q.device):
+        check(lib.b200_fa2_bwd_desc(desc, q.data_ptr(), k.data_ptr(), v.data_ptr(), O.data_ptr(), L.data_ptr(), dO.data_ptr(),
+                                    dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), None, 0, _stream()), "b200_fa2_bwd_desc")
+    return dQ, dK, dV
+
+
+class _FlashAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, causal, softmax_scale, layout):
+        O, L = attention_forward(q, k, v, causal, softmax_scale, layout)
+        ctx.save_for_backward(q, k, v, O, L)
+        ctx.cfg = (causal, softmax_scale, layout)
+        return O
+
+    @staticmethod
+    def backward(ctx, dO):
+        q, k, v, O, L = ctx.saved_tensors
+        causal, softmax_scale, layout = ctx.cfg
+        dQ, dK, dV = attention_backward(q, k, v, O, L, dO, causal, softmax_scale, layout)
+        return dQ, dK, dV, None, None, None
+
+
+def flash_attn_func(q, k, v, causal=False, softmax_scale=None, layout="bnhd"):
+    """Differentiable exact attention on the tcgen05 kernels.  q [B,Nq,H,d], k/v [B,Nkv,Hkv,d] (layout='bnhd', the
+    token-major order models use) or [B,H,N,d] (layout='bhnd'); any batch/head/row strides with a contiguous last
+    dimension (e.g. slices of a packed qkv projection); Hkv may divide H (GQA / MQA)."""
+    return _FlashAttnFn.apply(q, k, v, causal, softmax_scale, layout)

@@ -284,6 +284,69 @@ int b200_fa2_bwd_ex(const void* Q, const void* K, const void* V, const void* O, 
     return bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, B * H, Nq, Nkv, d, scale, dtype, ws, ws_bytes, st, flags);
 }
 
+static bool lay_is_zero(const b200_layout& l) { return l.batch_stride == 0 && l.head_stride == 0 && l.row_stride == 0; }
+static Lay lay_of(const b200_layout& l, int H, int N, int d)
+{
+    return lay_is_zero(l) ? lay_contiguous(H, N, d) : Lay{l.batch_stride, l.head_stride, l.row_stride};
+}
+static bool lay_is_contiguous(const b200_layout& l, int H, int N, int d)
+{
+    const Lay c = lay_contiguous(H, N, d);
+    return lay_is_zero(l) || (l.batch_stride == c.sb && l.head_stride == c.sh && l.row_stride == c.sn);
+}
+static int desc_check(const b200_attn_desc* p)
+{
+    if (!p || !valid_dtype(p->dtype) || p->B < 0 || p->H < 0 || p->Nq < 0 || p->Nkv < 0 || p->d <= 0) return B200_ERR_INVALID_ARGUMENT;
+    if (p->H > 0 && (p->Hkv < 1 || p->Hkv > p->H || p->H % p->Hkv != 0)) return B200_ERR_INVALID_ARGUMENT;
+    if ((p->flags & ~B200_FLAG_CAUSAL) != 0 || ((p->flags & B200_FLAG_CAUSAL) && p->Nq > p->Nkv)) return B200_ERR_INVALID_ARGUMENT;
+    if ((long long)p->B * p->H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
+    return B200_OK;
+}
+
+int b200_fa2_fwd_desc(const b200_attn_desc* p, const void* Q, const void* K, const void* V, void* O, float* L, cudaStream_t st)
+{
+    B200_TRY(desc_check(p));
+    const bool plain = p->Hkv == p->H && lay_is_contiguous(p->q, p->H, p->Nq, p->d) && lay_is_contiguous(p->o, p->H, p->Nq, p->d) &&
+                       lay_is_contiguous(p->k, p->H, p->Nkv, p->d) && lay_is_contiguous(p->v, p->H, p->Nkv, p->d);
+    if (plain) return fwd_impl(Q, K, V, O, L, p->B * p->H, p->Nq, p->Nkv, p->d, p->scale, p->dtype, st, p->flags);
+    if ((size_t)p->B * p->H == 0 || (p->Nq == 0 && p->Nkv == 0)) return B200_OK;
+    if (p->Nq == 0 || p->Nkv == 0 || !Q || !K || !V || !O || !L) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    const bool causal = (p->flags & B200_FLAG_CAUSAL) != 0;
+    FwdArgs a{Q, K, V, O, L, lay_of(p->q, p->H, p->Nq, p->d), lay_of(p->k, p->Hkv, p->Nkv, p->d), lay_of(p->v, p->Hkv, p->Nkv, p->d),
+              lay_of(p->o, p->H, p->Nq, p->d), (long long)p->Nq, p->B, p->H, p->Hkv, p->Nq, p->Nkv, p->d,
+              resolve_scale(p->scale, p->d), p->dtype, causal};
+    return tc_fwd_strided(a, st);
+}
+
+int b200_fa2_bwd_desc(const b200_attn_desc* p, const void* Q, const void* K, const void* V, const void* O, const float* L,
+                      const void* dO, void* dQ, void* dK, void* dV, void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    B200_TRY(desc_check(p));
+    const int H = p->H, d = p->d;
+    const bool plain = p->Hkv == H && lay_is_contiguous(p->q, H, p->Nq, d) && lay_is_contiguous(p->o, H, p->Nq, d) &&
+                       lay_is_contiguous(p->d_o, H, p->Nq, d) && lay_is_contiguous(p->dq, H, p->Nq, d) &&
+                       lay_is_contiguous(p->k, H, p->Nkv, d) && lay_is_contiguous(p->v, H, p->Nkv, d) &&
+                       lay_is_contiguous(p->dk, H, p->Nkv, d) && lay_is_contiguous(p->dv, H, p->Nkv, d);
+    if (plain) return bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, p->B * H, p->Nq, p->Nkv, d, p->scale, p->dtype, ws, ws_bytes, st, p->flags);
+    if ((size_t)p->B * H == 0 || (p->Nq == 0 && p->Nkv == 0)) return B200_OK;
+    if (p->Nq == 0 || p->Nkv == 0 || !Q || !K || !V || !O || !L || !dO || !dQ || !dK || !dV) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    if (!tc_bwd_supported(p->dtype, d, p->Nq, p->Nkv)) return B200_ERR_UNSUPPORTED;
+    const int BH = p->B * H;
+    const size_t need = bwd_ws_bytes(BH, p->Nq, p->Nkv, d, p->dtype);
+    if (ws == nullptr) B200_TRY(arena_get(need, &ws));
+    else if (ws_bytes < need) return B200_ERR_WORKSPACE;
+    float* D = reinterpret_cast<float*>(ws);
+    const size_t dbytes = (((size_t)BH * p->Nq * sizeof(float)) + 255) & ~(size_t)255;
+    const Lay lo = lay_of(p->o, H, p->Nq, d), ldo = lay_of(p->d_o, H, p->Nq, d);
+    B200_TRY(rowdot_strided(dO, O, ldo, lo, D, p->B, H, p->Nq, d, p->dtype, st));
+    BwdArgs a{Q, K, V, dO, L, D, dQ, dK, dV, lay_of(p->q, H, p->Nq, d), lay_of(p->k, p->Hkv, p->Nkv, d), lay_of(p->v, p->Hkv, p->Nkv, d),
+              ldo, lay_of(p->dq, H, p->Nq, d), lay_of(p->dk, p->Hkv, p->Nkv, d), lay_of(p->dv, p->Hkv, p->Nkv, d),
+              p->B, H, p->Hkv, p->Nq, p->Nkv, d, resolve_scale(p->scale, d), p->dtype, (p->flags & B200_FLAG_CAUSAL) != 0};
+    return tc_bwd_strided(a, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
+}
+
 size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
 {
     if (B <= 0 || H <= 0 || Nq <= 0 || Nkv <= 0 || d <= 0 || !valid_dtype(dtype)) return 0;

@@ -72,7 +72,7 @@ __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
 // a load issued on the critical path queues behind operand traffic for hundreds of cycles.
 __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* smem, uint64_t* bar_in_full,
                                                  uint64_t* bar_S, uint64_t* bar_dP, uint64_t* bar_P, uint64_t* bar_dS,
-                                                 int n_it, int qt_min, int i_off, int kv0, int causal,
+                                                 int n_tot, int n_it, int qt_min, int i_off, int kv0, int causal,
                                                  float scale_log2, float scale)
 {
     using namespace bwd;
@@ -80,7 +80,7 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
     const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
     const bool lane0 = (threadIdx.x & 31) == 0;
     const uint32_t stat_base = smem_u32(smem + OFF_STAT) + 128 * w;    // + s * 2 * STAT_BYTES (+ STAT_BYTES for D)
-    for (int i = 0; i < n_it; ++i) {
+    for (int i = 0, ii = 0; i < n_tot; ++i) {
         const int b = i & 1, s = i % NS;
         const uint32_t tS = tmem + TM_S + 64 * b + 32 * w + lane_base;
         const uint32_t tP = tmem + TM_DP + 32 * w + lane_base;
@@ -101,7 +101,7 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
         if (causal) {
             // key kv0 + r is hidden from the queries before it: only the two q tiles on the diagonal are affected
-            int qt = i + i_off;
+            int qt = ii + i_off;
             if (qt >= n_it) qt -= n_it;
             const int first_visible = kv0 + r - (qt_min + qt) * BM - 32 * w;   // column (of this warpgroup's 32) of query kv0 + r
             if (first_visible > 0) {
@@ -149,6 +149,7 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         __syncwarp();
         if (lane0) mbar_arrive(bar_dS);
         B200_TRB(0, i, 3);
+        if (++ii == n_it) ii = 0;                                       // next q head of the group
     }
 }
 
@@ -157,17 +158,19 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
 // instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
 template <int DR>
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
-                                               float* __restrict__ dQacc, int Nq, int n_it, int qt_min, int i_off, int bh,
-                                               int dbg)
+                                               float* __restrict__ dQacc, int Nq, int n_tot, int n_it, int qt_min, int i_off,
+                                               size_t bhq0, int dbg)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
     const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
     const bool lane0 = (threadIdx.x & 31) == 0;
-    for (int i = 0; i < n_it; ++i) {
-        int qt = i + i_off;                                            // the q tile this iteration works on
+    for (int i = 0, ii = 0, g = 0; i < n_tot; ++i) {
+        int qt = ii + i_off;                                           // the q tile this iteration works on
         if (qt >= n_it) qt -= n_it;
         qt += qt_min;
+        const size_t bh = bhq0 + g;                                    // q head g of this K/V head's group
+        if (++ii == n_it) { ii = 0; ++g; }
         mbar_wait(bar_dQ_full, i & 1);
         tc_fence_after();
         B200_TRB(1, i, 0);
@@ -179,7 +182,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         __syncwarp();
         if (lane0) mbar_arrive(bar_dQ_empty);                          // TMEM columns are free again
         B200_TRB(1, i, 1);
-        float* dst = dQacc + ((size_t)bh * Nq + (size_t)qt * BM) * DR + r;
+        float* dst = dQacc + (bh * Nq + (size_t)qt * BM) * DR + r;
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
         if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
             if (q_valid == BM) {
@@ -196,7 +199,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
 
 // dV (w = 0) / dK (w = 1) epilogue: TMEM fp32 [128 kv x 128 d] -> bf16 -> swizzled smem -> TMA store.
 template <int DR>
-__device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem, const CUtensorMap* tm, int kv0, int bh)
+__device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem, const CUtensorMap* tm, int kv0, int hk, int b)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;
@@ -221,8 +224,8 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
     fence_proxy_async_smem();
     named_bar_sync(4 + w, 128);
     if (r == 0) {
-        tma_store_3d(tm, out, 0, kv0, bh);
-        if (DR == 128) tma_store_3d(tm, out + KV_BOX, 64, kv0, bh);
+        tma_store_4d(tm, out, 0, kv0, hk, b);
+        if (DR == 128) tma_store_4d(tm, out + KV_BOX, 64, kv0, hk, b);
         tma_store_commit();
         tma_store_wait<0>();
     }
@@ -237,7 +240,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
            float* __restrict__ dQacc, const __grid_constant__ CUtensorMap tmdK,
            const __grid_constant__ CUtensorMap tmdV, const float* __restrict__ L2p, const float* __restrict__ Dp,
-           int Nq, int Nq_pad, float scale_log2, float scale, int dbg, int causal)
+           int Nq, int Nq_pad, float scale_log2, float scale, int dbg, int causal, int G, int BHkv)
 {
     using namespace bwd;
     extern __shared__ uint8_t smem_raw[];
@@ -256,7 +259,11 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
 
     const int warp = threadIdx.x >> 5;
-    const int bh = blockIdx.y, kv0 = blockIdx.x * BN;
+    // grid (kv tiles, K/V heads of the map, batches of the map).  One CTA serves its K/V tile for all G query heads of
+    // the group (grouped-query attention; G = 1: MHA): dK/dV simply keep accumulating over the group's q tiles.
+    const int hk = blockIdx.y, b = blockIdx.z, kv0 = blockIdx.x * BN;
+    if (b * (int)gridDim.y + hk >= BHkv) return;                    // (ragged last batch of a re-split contiguous BH)
+    const size_t bhq0 = ((size_t)b * gridDim.y + hk) * G;            // first q head of the group, in [B*H)
     const int n_q = (Nq + BM - 1) / BM;
     // Every CTA of a (b,h) slab walks the q tiles in the same cyclic order but starts at a different
     // one: at any moment the CTAs that run together reduce-add into DIFFERENT dQ tiles, so their
@@ -266,6 +273,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     const int qt_min = causal ? min(kv0 / BM, n_q - 1) : 0;
     const int n_it = n_q - qt_min;
     const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x) % n_it;
+    const int n_tot = G * n_it;
 
     if (threadIdx.x == 0) {
         mbar_init(bar_KV, 1);
@@ -293,22 +301,24 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         // ================================ TMA producer ================================
         if (elect_one()) {
             mbar_expect_tx(bar_KV, 2 * NBOX * KV_BOX);
-            for (int b = 0; b < NBOX; ++b) {
-                tma_load_3d(smem + OFF_K + b * KV_BOX, &tmK, bar_KV, b * 64, kv0, bh, kEvictFirst);
-                tma_load_3d(smem + OFF_V + b * KV_BOX, &tmV, bar_KV, b * 64, kv0, bh, kEvictFirst);
+            for (int bx = 0; bx < NBOX; ++bx) {
+                tma_load_4d(smem + OFF_K + bx * KV_BOX, &tmK, bar_KV, bx * 64, kv0, hk, b, kEvictFirst);
+                tma_load_4d(smem + OFF_V + bx * KV_BOX, &tmV, bar_KV, bx * 64, kv0, hk, b, kEvictFirst);
             }
-            const float* Lrow = L2p + (size_t)bh * Nq_pad;
-            const float* Drow = Dp + (size_t)bh * Nq_pad;
-            for (int i = 0; i < n_it; ++i) {
+            for (int i = 0, ii = 0, g = 0; i < n_tot; ++i) {
                 const int s = i % NS;
-                int qt = i + i_off;
+                int qt = ii + i_off;
                 if (qt >= n_it) qt -= n_it;
                 qt += qt_min;
+                const int h = hk * G + g;
+                const float* Lrow = L2p + (bhq0 + g) * Nq_pad;
+                const float* Drow = Dp + (bhq0 + g) * Nq_pad;
+                if (++ii == n_it) { ii = 0; ++g; }
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
                 mbar_expect_tx(&bar_in_full[s], 2 * NBOX * Q_BOX + 2 * STAT_BYTES);
-                for (int b = 0; b < NBOX; ++b) {
-                    tma_load_3d(smem + OFF_Q + s * Q_TILE + b * Q_BOX, &tmQ, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
-                    tma_load_3d(smem + OFF_DO + s * Q_TILE + b * Q_BOX, &tmdO, &bar_in_full[s], b * 64, qt * BM, bh, kEvictLast);
+                for (int bx = 0; bx < NBOX; ++bx) {
+                    tma_load_4d(smem + OFF_Q + s * Q_TILE + bx * Q_BOX, &tmQ, &bar_in_full[s], bx * 64, qt * BM, h, b, kEvictLast);
+                    tma_load_4d(smem + OFF_DO + s * Q_TILE + bx * Q_BOX, &tmdO, &bar_in_full[s], bx * 64, qt * BM, h, b, kEvictLast);
                 }
                 bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES, Lrow + qt * BM, STAT_BYTES, &bar_in_full[s]);
                 bulk_load_1d(smem + OFF_STAT + s * 2 * STAT_BYTES + STAT_BYTES, Drow + qt * BM, STAT_BYTES, &bar_in_full[s]);
@@ -342,9 +352,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             mbar_wait(&bar_in_full[0], 0);
             tc_fence_after();
             M1(0); M2(0);
-            for (int i = 0; i < n_it; ++i) {
+            for (int i = 0; i < n_tot; ++i) {
                 const int b = i & 1, s = i % NS;
-                if (i + 1 < n_it) {
+                if (i + 1 < n_tot) {
                     mbar_wait(&bar_in_full[(i + 1) % NS], ((i + 1) / NS) & 1);
                     tc_fence_after();
                     M1(i + 1);
@@ -360,7 +370,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 B200_TRB(2, i, 3);
                 mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
                 umma_commit(&bar_in_empty[s]);
-                if (i + 1 < n_it) M2(i + 1);
+                if (i + 1 < n_tot) M2(i + 1);
                 B200_TRB(2, i, 4);
                 mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
                 tc_fence_after();
@@ -379,12 +389,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         }
     } else if (warp >= 4 && warp < 12) {
         const int w = (warp - 4) >> 2;
-        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_it, qt_min, i_off, kv0, causal, scale_log2, scale);
+        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_tot, n_it, qt_min, i_off, kv0, causal, scale_log2, scale);
         mbar_wait(bar_done, 0);
         tc_fence_after();
-        bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, bh);
+        bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, hk, b);
     } else if (warp >= 12) {
-        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_it, qt_min, i_off, bh, dbg);
+        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_tot, n_it, qt_min, i_off, bhq0, dbg);
     }
 
     tc_fence_before();
@@ -421,6 +431,26 @@ cast_dq_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, s
     }
 }
 
+// fp32 accumulator [B*H, Nq, d] (contiguous) -> bf16 dQ with arbitrary batch / head / row strides; one warp per row
+__global__ void __launch_bounds__(256)
+cast_dq_strided_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, Lay lay, int H, int Nq, int d, size_t rows)
+{
+    const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const size_t bh = row / Nq;
+    const int n = (int)(row - bh * Nq), b = (int)(bh / H), h = (int)(bh - (size_t)b * H);
+    const float* src = acc + row * d;
+    __nv_bfloat16* dst = out + (size_t)b * lay.sb + (size_t)h * lay.sh + (size_t)n * lay.sn;
+    for (int c = lane * 4; c < d; c += 128) {
+        const float4 a = *reinterpret_cast<const float4*>(src + c);
+        uint2 o;
+        o.x = pack_bf16x2(a.x, a.y);
+        o.y = pack_bf16x2(a.z, a.w);
+        *reinterpret_cast<uint2*>(dst + c) = o;
+    }
+}
+
 #ifdef B200_TRACE
 int bwd_trace_read(long long* out, int n)
 {
@@ -444,10 +474,16 @@ size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype)
     return 2 * al256((size_t)BH * Nq_pad * sizeof(float)) + al256((size_t)BH * Nq * d * sizeof(float));
 }
 
+// One launch: (dK, dV) of every K/V head and the fp32 dQ contributions of its G query heads.
+struct BwdLaunch {
+    const void *Q, *K, *V, *dO; const float *L2p, *Dp; float* dQacc; void *dK, *dV;
+    Lay lq, lk, lv, ldo, ldk, ldv;
+    int Bm, Hkv, G, BHkv;            // grid / map batches and K/V heads, group size, valid K/V slabs (<= Bm * Hkv)
+    int Nq, Nkv; float scale; bool causal;
+};
+
 template <int DR>
-static int bwd_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
-                      float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st,
-                      bool causal = false)
+static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 {
     using namespace bwd;
     static bool attr_set = false;
@@ -455,18 +491,63 @@ static int bwd_launch(const void* Q, const void* K, const void* V, const void* d
         B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         attr_set = true;
     }
-    const int Nq_pad = (Nq + 63) / 64 * 64;
+    const int Nq_pad = (a.Nq + 63) / 64 * 64, Hq = a.Hkv * a.G;
     CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
     const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-    if (make_tmap_3d(&tmQ, Q, bf, 2, BH, Nq, DR, BM, 64) || make_tmap_3d(&tmdO, dO, bf, 2, BH, Nq, DR, BM, 64) ||
-        make_tmap_3d(&tmK, K, bf, 2, BH, Nkv, DR, BN, 64) || make_tmap_3d(&tmV, V, bf, 2, BH, Nkv, DR, BN, 64) ||
-        make_tmap_3d(&tmdK, dK, bf, 2, BH, Nkv, DR, BN, 64) || make_tmap_3d(&tmdV, dV, bf, 2, BH, Nkv, DR, BN, 64))
+    if (make_tmap_4d(&tmQ, a.Q, bf, 2, a.Bm, Hq, a.Nq, DR, a.lq.sb, a.lq.sh, a.lq.sn, BM, 64) ||
+        make_tmap_4d(&tmdO, a.dO, bf, 2, a.Bm, Hq, a.Nq, DR, a.ldo.sb, a.ldo.sh, a.ldo.sn, BM, 64) ||
+        make_tmap_4d(&tmK, a.K, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lk.sb, a.lk.sh, a.lk.sn, BN, 64) ||
+        make_tmap_4d(&tmV, a.V, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lv.sb, a.lv.sh, a.lv.sn, BN, 64) ||
+        make_tmap_4d(&tmdK, a.dK, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldk.sb, a.ldk.sh, a.ldk.sn, BN, 64) ||
+        make_tmap_4d(&tmdV, a.dV, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldv.sb, a.ldv.sh, a.ldv.sn, BN, 64))
         return B200_ERR_CUDA;
-    dim3 grid((Nkv + BN - 1) / BN, BH);
+    dim3 grid((a.Nkv + BN - 1) / BN, a.Hkv, a.Bm);
     static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
     if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
-    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, dQacc, tmdK, tmdV, L2p, Dp, Nq, Nq_pad,
-                                            scale * 1.4426950408889634f, scale, dbg, causal ? 1 : 0);
+    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq, Nq_pad,
+                                                a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
+// contiguous [BH, N, 128 or 64] slabs (the reference layout); BH is cut into (batches x heads) that fit the grid limits
+static BwdLaunch contiguous_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
+                                   float* dQacc, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, bool causal)
+{
+    const int Hm = BH <= 65535 ? BH : 32768, Bm = (BH + Hm - 1) / Hm;
+    const Lay q = lay_contiguous(Hm, Nq, d), k = lay_contiguous(Hm, Nkv, d);
+    return BwdLaunch{Q, K, V, dO, L2p, Dp, dQacc, dK, dV, q, k, k, q, k, k, Bm, Hm, 1, BH, Nq, Nkv, scale, causal};
+}
+
+// padded statistics + zeroed fp32 dQ accumulator in the workspace, one launch, then the cast (strided when dQ is)
+static int bwd_run(const BwdLaunch& a, int BHq, int d, void* ws, void* dQ, const Lay* ldq, int B, int H,
+                   const float* L, const float* Dvec, cudaStream_t st)
+{
+    using namespace bwd;
+    const int Nq = a.Nq, Nq_pad = (Nq + 63) / 64 * 64;
+    uint8_t* p = reinterpret_cast<uint8_t*>(ws);
+    float* L2p = reinterpret_cast<float*>(p); p += al256((size_t)BHq * Nq_pad * sizeof(float));
+    float* Dp = reinterpret_cast<float*>(p);  p += al256((size_t)BHq * Nq_pad * sizeof(float));
+    float* dQacc = reinterpret_cast<float*>(p);
+    const size_t n_dq = (size_t)BHq * Nq * d;
+    const size_t total = (size_t)BHq * Nq_pad;
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
+    BwdLaunch b = a;
+    b.L2p = L2p; b.Dp = Dp; b.dQacc = dQacc;
+    if (d == 128) B200_TRY(bwd_launch<128>(b, st)); else B200_TRY(bwd_launch<64>(b, st));
+    if (ldq == nullptr) {
+        unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
+        if (cgrid > 148u * 8) cgrid = 148u * 8;
+        cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);
+    } else {
+        const size_t rows = (size_t)BHq * Nq;
+        cast_dq_strided_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), *ldq, H, Nq, d, rows);
+        (void)B;
+    }
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
@@ -476,32 +557,27 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
            void* ws, size_t ws_bytes, cudaStream_t st, bool causal)
 {
-    using namespace bwd;
     if (causal && Nq != Nkv) return B200_ERR_UNSUPPORTED;
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
-    if ((align & 15) != 0 || BH > 65535)
+    if ((align & 15) != 0)
         return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
     if (ws_bytes < tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype)) return B200_ERR_WORKSPACE;
-    const int Nq_pad = (Nq + 63) / 64 * 64;
-    uint8_t* p = reinterpret_cast<uint8_t*>(ws);
-    float* L2p = reinterpret_cast<float*>(p); p += al256((size_t)BH * Nq_pad * sizeof(float));
-    float* Dp = reinterpret_cast<float*>(p);  p += al256((size_t)BH * Nq_pad * sizeof(float));
-    float* dQacc = reinterpret_cast<float*>(p);
-    const size_t n_dq = (size_t)BH * Nq * d;
+    const BwdLaunch a = contiguous_launch(Q, K, V, dO, nullptr, nullptr, nullptr, dK, dV, BH, Nq, Nkv, d, scale, causal);
+    return bwd_run(a, BH, d, ws, dQ, nullptr, 1, BH, L, Dvec, st);
+}
 
-    const size_t total = (size_t)BH * Nq_pad;
-    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
-    B200_CUDA_TRY(cudaGetLastError());
-    count_launch();
-    B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
-    if (d == 128) B200_TRY(bwd_launch<128>(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
-    else B200_TRY(bwd_launch<64>(Q, K, V, dO, L2p, Dp, dQacc, dK, dV, BH, Nq, Nkv, scale, st, causal));
-    unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
-    if (cgrid > 148u * 8) cgrid = 148u * 8;
-    cast_dq_kernel<<<cgrid, 256, 0, st>>>(dQacc, reinterpret_cast<__nv_bfloat16*>(dQ), n_dq / 4);
-    B200_CUDA_TRY(cudaGetLastError());
-    count_launch();
-    return B200_OK;
+// strided / grouped-head form: L, D contiguous [B*H, Nq]; workspace as tc_bwd_workspace_bytes(B*H, ...)
+int tc_bwd_strided(const BwdArgs& g, void* ws, size_t ws_bytes, cudaStream_t st)
+{
+    if (!tc_bwd_supported(g.dtype, g.d, g.Nq, g.Nkv)) return B200_ERR_UNSUPPORTED;
+    if (g.causal && g.Nq != g.Nkv) return B200_ERR_UNSUPPORTED;
+    if (g.B < 1 || g.H < 1 || g.Hkv < 1 || g.H % g.Hkv != 0 || g.B > 65535 || g.H > 65535) return B200_ERR_INVALID_ARGUMENT;
+    const uintptr_t align = (uintptr_t)g.Q | (uintptr_t)g.K | (uintptr_t)g.V | (uintptr_t)g.dO | (uintptr_t)g.dQ | (uintptr_t)g.dK | (uintptr_t)g.dV;
+    if ((align & 15) != 0 || (g.ldq.sn & 3) || (g.ldq.sh & 3) || (g.ldq.sb & 3)) return B200_ERR_UNSUPPORTED;
+    if (ws_bytes < tc_bwd_workspace_bytes(g.B * g.H, g.Nq, g.Nkv, g.d, g.dtype)) return B200_ERR_WORKSPACE;
+    const BwdLaunch a{g.Q, g.K, g.V, g.dO, nullptr, nullptr, nullptr, g.dK, g.dV, g.lq, g.lk, g.lv, g.ldo, g.ldk, g.ldv,
+                      g.B, g.Hkv, g.H / g.Hkv, g.B * g.Hkv, g.Nq, g.Nkv, g.scale, g.causal};
+    return bwd_run(a, g.B * g.H, g.d, ws, g.dQ, &g.ldq, g.B, g.H, g.L, g.D, st);
 }
 
 // ---- pieces for the ring backward: statistics once per call; per ring step one launch that adds
@@ -534,7 +610,8 @@ int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO
     const int Nq_pad = (Nq + 63) / 64 * 64;
     const float* L2p = reinterpret_cast<const float*>(stats);
     const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
-    return bwd_launch<128>(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, scale, st);
+    const BwdLaunch a = contiguous_launch(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, 128, scale, false);
+    return bwd_launch<128>(a, st);
 }
 
 }  // namespace b200

@@ -31,6 +31,23 @@ void count_launch(int n = 1);       // bookkeeping for b200_debug_launch_count()
 // coff = Nkv - Nq (bottom-right aligned) when causal and kNoCausal otherwise.
 constexpr int kNoCausal = 0x3fffffff;
 
+// ---- tensor layouts of the extended entry points ---------------------------------------------------
+// Element strides of a [B, H, N, d] tensor whose last dimension is contiguous: the reference's contiguous slabs,
+// token-major [B, N, H, d] views, row sub-blocks (ring steps) and grouped K/V heads are all instances.
+struct Lay { long long sb, sh, sn; };
+inline Lay lay_contiguous(int H, int N, int d) { return Lay{(long long)H * N * d, (long long)N * d, (long long)d}; }
+struct FwdArgs {
+    const void *Q, *K, *V; void* O; float* L;      // L: [B*H rows of ldL floats], row (b*H + h) starts at L + (b*H + h) * ldL
+    Lay lq, lk, lv, lo; long long ldL;
+    int B, H, Hkv, Nq, Nkv, d; float scale; int dtype; bool causal;
+};
+struct BwdArgs {
+    const void *Q, *K, *V, *dO; const float *L, *D;   // L, D contiguous [B*H, Nq]
+    void *dQ, *dK, *dV;
+    Lay lq, lk, lv, ldo, ldq, ldk, ldv;
+    int B, H, Hkv, Nq, Nkv, d; float scale; int dtype; bool causal;
+};
+
 // ---- generic CUDA-core kernels (generic_simt.cu) ------------------------------------------------
 // mode 0: O + LSE (L may be NULL);  mode 1: O + l (into L) + m (into M)   [FA1 API]
 int simt_fwd(const void* Q, const void* K, const void* V, void* O, float* L, float* M, int BH, int Nq, int Nkv, int d,
@@ -40,6 +57,8 @@ int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtyp
 int simt_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
              void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype, cudaStream_t st,
              int coff = kNoCausal);
+int rowdot_strided(const void* dO, const void* O, const Lay& ldo, const Lay& lo, float* D, int B, int H, int N, int d, int dtype,
+                   cudaStream_t st);
 int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st);
 // (O, L) = merge of n partials at Op + s * o_stride (elements) / Lp + s * l_stride, plus (O, L) itself when `running`
 int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o_stride, size_t l_stride, int n, bool running,
@@ -49,11 +68,14 @@ int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv);
 int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
            float scale, int dtype, cudaStream_t st, bool causal = false);
+// strided / grouped-head form (tensor-core shapes only: tc_fwd_supported, 16-byte aligned bases and strides)
+int tc_fwd_strided(const FwdArgs& a, cudaStream_t st);
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
            void* ws, size_t ws_bytes, cudaStream_t st, bool causal = false);
+int tc_bwd_strided(const BwdArgs& a, void* ws, size_t ws_bytes, cudaStream_t st);
 
 // ring backward building blocks (bf16, d = 128): padded statistics once, then accumulate-only steps
 bool tc_bwd_ring_supported(int dtype, int d, int BH, const void* Q, const void* K, const void* V, const void* dO);

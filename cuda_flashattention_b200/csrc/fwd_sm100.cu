@@ -86,8 +86,8 @@ constexpr float kRescaleThreshold = 8.0f;
 template <class C>
 __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, uint64_t* bar_S, uint64_t* bar_Pa,
                                              uint64_t* bar_Pb, uint64_t* bar_O, const CUtensorMap* tmO,
-                                             float* __restrict__ Lout, int Nq, int Nkv, int nkv, int n_plain,
-                                             int causal, int q0, int bh, float scale_log2)
+                                             float* __restrict__ Lout, long long ldL, int Nq, int Nkv, int nkv, int n_plain,
+                                             int causal, int q0, int h, int b, int bh, float scale_log2)
 {
     constexpr int BC = C::BC, D = C::D;
     const int wg_thread = threadIdx.x & 127;                       // == TMEM lane == row within the tile
@@ -241,20 +241,20 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     named_bar_sync(1 + t, 128);
     if (wg_thread == 0) {
 #pragma unroll
-        for (int b = 0; b < C::BOXES; ++b) tma_store_3d(tmO, sO + b * C::Q_BOX, b * C::CPB, q0 + t * 128, bh);
+        for (int bx = 0; bx < C::BOXES; ++bx) tma_store_4d(tmO, sO + bx * C::Q_BOX, bx * C::CPB, q0 + t * 128, h, b);
         tma_store_commit();
         tma_store_wait<0>();
     }
     const int row = q0 + t * 128 + r;
     if (Lout != nullptr && row < Nq)
-        Lout[(size_t)bh * Nq + row] = (m + log2f(l)) * 0.6931471805599453f;
+        Lout[(size_t)bh * ldL + row] = (m + log2f(l)) * 0.6931471805599453f;
 }
 
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
 fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-           float* __restrict__ Lout, int Nq, int Nkv, float scale_log2, int causal)
+           float* __restrict__ Lout, long long ldL, int Nq, int Nkv, float scale_log2, int causal, int G, int BH)
 {
     constexpr int NT = C::NT, BC = C::BC, D = C::D, ST = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -275,7 +275,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_Ve + ST);
 
     const int warp = threadIdx.x >> 5;
-    const int bh = blockIdx.y;
+    // grid (q blocks, heads of the map, batches of the map); K/V head = h / G (grouped-query attention, G = 1: MHA)
+    const int h = blockIdx.y, b = blockIdx.z, bh = b * gridDim.y + h, hk = h / G;
+    if (bh >= BH) return;                                          // (a re-split contiguous BH may leave the last batch ragged)
     // causal (Nq == Nkv): the q blocks near the end of the sequence have the most K/V tiles -- schedule them first
     const int q0 = (causal ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * (NT * 128);
     const int ntiles = min(NT, (Nq - q0 + 127) / 128);
@@ -304,20 +306,20 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         if (elect_one()) {
             for (int t = 0; t < ntiles; ++t) {
                 mbar_expect_tx(&bar_Q[t], C::Q_TILE);
-                for (int b = 0; b < C::BOXES; ++b)
-                    tma_load_3d(sQ + t * C::Q_TILE + b * C::Q_BOX, &tmQ, &bar_Q[t], b * C::CPB, q0 + t * 128, bh, kEvictFirst);
+                for (int bx = 0; bx < C::BOXES; ++bx)
+                    tma_load_4d(sQ + t * C::Q_TILE + bx * C::Q_BOX, &tmQ, &bar_Q[t], bx * C::CPB, q0 + t * 128, h, b, kEvictFirst);
             }
             for (int j = 0; j < nkv; ++j) {
                 const int s = j % ST;
                 const uint32_t ph = (j / ST) & 1;
                 mbar_wait(&bar_Ke[s], ph ^ 1);
                 mbar_expect_tx(&bar_Kf[s], C::KV_TILE);
-                for (int b = 0; b < C::BOXES; ++b)
-                    tma_load_3d(sK + s * C::KV_TILE + b * C::KV_BOX, &tmK, &bar_Kf[s], b * C::CPB, j * BC, bh, kEvictLast);
+                for (int bx = 0; bx < C::BOXES; ++bx)
+                    tma_load_4d(sK + s * C::KV_TILE + bx * C::KV_BOX, &tmK, &bar_Kf[s], bx * C::CPB, j * BC, hk, b, kEvictLast);
                 mbar_wait(&bar_Ve[s], ph ^ 1);
                 mbar_expect_tx(&bar_Vf[s], C::KV_TILE);
-                for (int b = 0; b < C::BOXES; ++b)
-                    tma_load_3d(sV + s * C::KV_TILE + b * C::KV_BOX, &tmV, &bar_Vf[s], b * C::CPB, j * BC, bh, kEvictLast);
+                for (int bx = 0; bx < C::BOXES; ++bx)
+                    tma_load_4d(sV + s * C::KV_TILE + bx * C::KV_BOX, &tmV, &bar_Vf[s], bx * C::CPB, j * BC, hk, b, kEvictLast);
             }
         }
     } else if (warp == 1) {
@@ -398,8 +400,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             const int nkv_t = nkv_of(t);
             // tiles entirely below the diagonal (and not the ragged last one) need no mask
             const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + 1) / BC, Nkv / BC)) : nkv_t - 1;
-            softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, Nq, Nkv, nkv_t, n_plain,
-                            causal, q0, bh, scale_log2);
+            softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, ldL, Nq, Nkv, nkv_t, n_plain,
+                            causal, q0, h, b, bh, scale_log2);
         }
     }
 
@@ -410,8 +412,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 
 // ------------------------------------------------------------------------------------ host side
 template <class C>
-static int launch_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv,
-                      float scale, cudaStream_t st, bool causal)
+static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -420,21 +421,18 @@ static int launch_fwd(const void* Q, const void* K, const void* V, void* O, floa
     }
     const CUtensorMapDataType dt = C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     const CUtensorMapSwizzle v_swz = C::kF32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
-    const float scale_log2 = scale * 1.4426950408889634f;
-    for (int bh0 = 0; bh0 < BH; bh0 += 65535) {
-        const int nbh = (BH - bh0) < 65535 ? (BH - bh0) : 65535;
-        const size_t qoff = (size_t)bh0 * Nq * C::D * C::EB, koff = (size_t)bh0 * Nkv * C::D * C::EB;
-        CUtensorMap tmQ, tmK, tmV, tmO;
-        if (make_tmap_3d(&tmQ, (const uint8_t*)Q + qoff, dt, C::EB, nbh, Nq, C::D, 128, C::CPB) ||
-            make_tmap_3d(&tmK, (const uint8_t*)K + koff, dt, C::EB, nbh, Nkv, C::D, C::BC, C::CPB) ||
-            make_tmap_3d(&tmV, (const uint8_t*)V + koff, dt, C::EB, nbh, Nkv, C::D, C::BC, C::CPB, v_swz) ||
-            make_tmap_3d(&tmO, (uint8_t*)O + qoff, dt, C::EB, nbh, Nq, C::D, 128, C::CPB))
-            return B200_ERR_CUDA;
-        dim3 grid((Nq + C::NT * 128 - 1) / (C::NT * 128), nbh);
-        fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, L ? L + (size_t)bh0 * Nq : nullptr, Nq, Nkv, scale_log2, causal ? 1 : 0);
-        B200_CUDA_TRY(cudaGetLastError());
+    const float scale_log2 = a.scale * 1.4426950408889634f;
+    CUtensorMap tmQ, tmK, tmV, tmO;
+    if (make_tmap_4d(&tmQ, a.Q, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lq.sb, a.lq.sh, a.lq.sn, 128, C::CPB) ||
+        make_tmap_4d(&tmK, a.K, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lk.sb, a.lk.sh, a.lk.sn, C::BC, C::CPB) ||
+        make_tmap_4d(&tmV, a.V, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lv.sb, a.lv.sh, a.lv.sn, C::BC, C::CPB, v_swz) ||
+        make_tmap_4d(&tmO, a.O, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::CPB))
+        return B200_ERR_CUDA;
+    dim3 grid((a.Nq + C::NT * 128 - 1) / (C::NT * 128), a.H, a.B);
+    fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
+                                                     a.H / a.Hkv, BH_valid);
+    B200_CUDA_TRY(cudaGetLastError());
     count_launch();
-    }
     return B200_OK;
 }
 
@@ -454,6 +452,26 @@ bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
     return d == 64 || d == 128;
 }
 
+static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
+{
+    if (a.dtype == B200_DTYPE_BF16) {
+        static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
+        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
+        if (a.d == 128) {
+            switch (variant) {
+#define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(a, BH_valid, st);
+                B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
+#undef B200_V
+                default: return B200_ERR_UNSUPPORTED;
+            }
+        }
+        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(a, BH_valid, st);
+    }
+    if (a.d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(a, BH_valid, st);
+    return launch_fwd<FwdCfg<float, 64, 2, 128>>(a, BH_valid, st);
+}
+
+// contiguous [BH, N, d] slabs (the reference layout)
 int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
            float scale, int dtype, cudaStream_t st, bool causal)
 {
@@ -461,21 +479,22 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
     if ((align & 15) != 0 || !(scale > 0.0f))      // TMA needs 16-byte bases; max(S)*scale needs scale > 0
         return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
-    if (dtype == B200_DTYPE_BF16) {
-        static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
-        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
-        if (d == 128) {
-            switch (variant) {
-#define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
-                B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
-#undef B200_V
-                default: return B200_ERR_UNSUPPORTED;
-            }
-        }
-        return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
-    }
-    if (d == 128) return launch_fwd<FwdCfg<float, 128, 1, 64>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
-    return launch_fwd<FwdCfg<float, 64, 2, 128>>(Q, K, V, O, L, BH, Nq, Nkv, scale, st, causal);
+    // the slabs are independent: cut BH into (batches x heads) that fit the grid limits; a ragged last batch is
+    // described by the map but its CTAs exit (bh >= BH)
+    const int Hm = BH <= 65535 ? BH : 32768, Bm = (BH + Hm - 1) / Hm;
+    FwdArgs a{Q, K, V, O, L, lay_contiguous(Hm, Nq, d), lay_contiguous(Hm, Nkv, d), lay_contiguous(Hm, Nkv, d),
+              lay_contiguous(Hm, Nq, d), (long long)Nq, Bm, Hm, Hm, Nq, Nkv, d, scale, dtype, causal};
+    return dispatch_fwd(a, BH, st);
+}
+
+int tc_fwd_strided(const FwdArgs& a, cudaStream_t st)
+{
+    if (!tc_fwd_supported(a.dtype, a.d, a.Nq, a.Nkv) || !(a.scale > 0.0f)) return B200_ERR_UNSUPPORTED;
+    if (a.causal && a.Nq != a.Nkv) return B200_ERR_UNSUPPORTED;
+    if (a.B < 1 || a.H < 1 || a.Hkv < 1 || a.H % a.Hkv != 0 || a.B > 65535 || a.H > 65535) return B200_ERR_INVALID_ARGUMENT;
+    const uintptr_t align = (uintptr_t)a.Q | (uintptr_t)a.K | (uintptr_t)a.V | (uintptr_t)a.O;
+    if ((align & 15) != 0) return B200_ERR_UNSUPPORTED;
+    return dispatch_fwd(a, a.B * a.H, st);
 }
 
 }  // namespace b200

@@ -136,6 +136,25 @@ rowdot_kernel(const T* __restrict__ dO, const T* __restrict__ O, float* __restri
     if (lane == 0) D[row] = s;
 }
 
+// D for strided [B, H, N, d] views (extended entry points); D itself is contiguous [B*H, N]
+template <typename T>
+__global__ void __launch_bounds__(256)
+rowdot_strided_kernel(const T* __restrict__ dO, const T* __restrict__ O, Lay ldo, Lay lo, float* __restrict__ D, int H, int N,
+                      int d, size_t rows)
+{
+    const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const size_t bh = row / N;
+    const int n = (int)(row - bh * N), b = (int)(bh / H), h = (int)(bh - (size_t)b * H);
+    const T* pa = dO + (size_t)b * ldo.sb + (size_t)h * ldo.sh + (size_t)n * ldo.sn;
+    const T* pb = O + (size_t)b * lo.sb + (size_t)h * lo.sh + (size_t)n * lo.sn;
+    float s = 0.0f;
+    for (int c = lane; c < d; c += 32) s = fmaf(ldf(pa + c), ldf(pb + c), s);
+    s = warp_sum(s);
+    if (lane == 0) D[row] = s;
+}
+
 // ---------------------------------------------------------------------------------------------
 // dQ.  grid = (ceil(Nq / kSimtWarps), B*H); one warp per query row, lanes = keys of the tile.
 // ---------------------------------------------------------------------------------------------
@@ -391,6 +410,19 @@ int rowdot(const void* dO, const void* O, float* D, size_t rows, int d, int dtyp
 {
     if (dtype == B200_DTYPE_F32) return rowdot_t((const float*)dO, (const float*)O, D, rows, d, st);
     return rowdot_t((const __nv_bfloat16*)dO, (const __nv_bfloat16*)O, D, rows, d, st);
+}
+
+int rowdot_strided(const void* dO, const void* O, const Lay& ldo, const Lay& lo, float* D, int B, int H, int N, int d, int dtype,
+                   cudaStream_t st)
+{
+    const size_t rows = (size_t)B * H * N;
+    if (rows == 0) return B200_OK;
+    const unsigned grid = (unsigned)((rows + 7) / 8);
+    if (dtype == B200_DTYPE_F32) rowdot_strided_kernel<float><<<grid, 256, 0, st>>>((const float*)dO, (const float*)O, ldo, lo, D, H, N, d, rows);
+    else rowdot_strided_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dO, (const __nv_bfloat16*)O, ldo, lo, D, H, N, d, rows);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
 }
 
 template <typename T>

@@ -118,6 +118,26 @@ B200_API int b200_fa2_bwd_ex(const void* Q, const void* K, const void* V, const 
                     void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
                     int flags, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+/* ---- descriptor entry points: strided layouts and grouped K/V heads (the callers' side) ----
+ * The reference stops at contiguous single-head [N,d] slabs (src/02_flash_attention_v2_forward/flash_attention_kernel.cu:300); models hold
+ * token-major [B,N,H,d] activations and share K/V heads between query heads (GQA / MQA).  A descriptor gives every
+ * tensor its batch / head / row stride in ELEMENTS (last dimension contiguous; all three zero = contiguous
+ * [B,H,N,d]), Hkv <= H with H % Hkv == 0 (query head h reads K/V head h / (H/Hkv); dK/dV are summed over the group),
+ * and the same flags as the _ex calls.  L (and the internal D) stay contiguous [B,H,Nq] fp32.
+ * Non-contiguous or grouped descriptors need the tensor-core shapes (d in {64,128}; backward bf16) and 16-byte
+ * aligned bases and strides; anything else returns B200_ERR_UNSUPPORTED (no silent slow path). */
+typedef struct b200_layout { long long batch_stride, head_stride, row_stride; } b200_layout;
+typedef struct b200_attn_desc {
+    int B, H, Hkv, Nq, Nkv, d, dtype, flags;
+    float scale;                                   /* 0 => 1/sqrt(d) */
+    b200_layout q, k, v, o, d_o, dq, dk, dv;       /* o is also the layout of O in the backward */
+} b200_attn_desc;
+B200_API int b200_fa2_fwd_desc(const b200_attn_desc* desc, const void* Q, const void* K, const void* V, void* O, float* L,
+                      cudaStream_t stream);
+B200_API int b200_fa2_bwd_desc(const b200_attn_desc* desc, const void* Q, const void* K, const void* V, const void* O,
+                      const float* L, const void* dO, void* dQ, void* dK, void* dV, void* workspace, size_t workspace_bytes,
+                      cudaStream_t stream);
+
 /* ---- host-buffer entry points --------------------------------------------------------------------
  * The reference's drivers own HOST arrays and copy them to the device around every call
  * (src/02_flash_attention_v2_forward/main.cu:42-64, src/02_flash_attention_v2_backward/main.cu:261-289).
