@@ -8,4 +8,4 @@ from .attention import (flash_attention_2_forward, flash_attention_2_backward, f
                         lse_merge_, uses_tensor_cores, flash_attention_2_forward_host,
                         flash_attention_2_forward_backward_host, attention_forward, attention_backward,
                         flash_attn_func)
-from .ring import RingComm, ring_attention_forward, ring_attention_backward, ring_kv_block  # noqa: F401
+from .ring import RingComm, ring_attention_forward, ring_attention_backward, ring_kv_block, zigzag_rows  # noqa: F401

@@ -63,6 +63,8 @@ _SIGS = {
     "b200_lse_merge": (_i, [_vp, _fp, _vp, _fp, _i, _i, _i, _i, _i, _vp]),
     "b200_ring_kv_block": (_i, [_i, _i, _i]),
     "b200_ring_fwd": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
+    "b200_ring_fwd_ex": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
+    "b200_ring_zigzag_chunk": (_i, [_i, _i, _i]),
     "b200_ring_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
     "b200_ring_unique_id": (_i, [_vp]),
     "b200_ring_comm_init": (_i, [C.POINTER(C.c_void_p), _vp, _i, _i]),

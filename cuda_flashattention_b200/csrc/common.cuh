@@ -61,8 +61,9 @@ int rowdot_strided(const void* dO, const void* O, const Lay& ldo, const Lay& lo,
                    cudaStream_t st);
 int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows, int d, int dtype, cudaStream_t st);
 // (O, L) = merge of n partials at Op + s * o_stride (elements) / Lp + s * l_stride, plus (O, L) itself when `running`
+// upper_mask (causal zigzag ring): partial s with bit s set only covers rows >= c of every Nl-row slab
 int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o_stride, size_t l_stride, int n, bool running,
-                    size_t rows, int d, int dtype, cudaStream_t st);
+                    size_t rows, int d, int dtype, cudaStream_t st, int Nl = 0, int c = 0, unsigned upper_mask = 0u);
 
 // ---- tcgen05 tensor-core kernels (fwd_sm100.cu / bwd_sm100.cu) ------------------------------------
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv);

@@ -324,17 +324,21 @@ lse_merge_kernel(T* __restrict__ Oa, float* __restrict__ La, const T* __restrict
 template <typename T>
 __global__ void __launch_bounds__(256)
 lse_merge_multi_kernel(T* __restrict__ O, float* __restrict__ L, const T* __restrict__ Op, const float* __restrict__ Lp,
-                       size_t o_stride, size_t l_stride, int n, int running, size_t rows, int d)
+                       size_t o_stride, size_t l_stride, int n, int running, size_t rows, int d, int Nl, int c,
+                       unsigned upper_mask)
 {
     const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const int lane = threadIdx.x & 31;
+    // causal zigzag ring: the partials in upper_mask only cover the rows >= c of every Nl-row slab
+    const unsigned skip = (upper_mask != 0u && (int)(row % (size_t)Nl) < c) ? upper_mask : 0u;
+    auto lse_of = [&](int s) { return ((skip >> s) & 1u) ? -INFINITY : Lp[s * l_stride + row]; };
     float mx = running ? L[row] : -INFINITY;
-    for (int s = 0; s < n; ++s) mx = fmaxf(mx, Lp[s * l_stride + row]);
+    for (int s = 0; s < n; ++s) mx = fmaxf(mx, lse_of(s));
     float tot = 0.f;
     if (mx != -INFINITY) {
         if (running) tot += expf(L[row] - mx);
-        for (int s = 0; s < n; ++s) tot += expf(Lp[s * l_stride + row] - mx);
+        for (int s = 0; s < n; ++s) tot += expf(lse_of(s) - mx);
     }
     const float inv = tot > 0.f ? 1.0f / tot : 0.f;
     for (int c = lane * 4; c < d; c += 128) {
@@ -345,7 +349,8 @@ lse_merge_multi_kernel(T* __restrict__ O, float* __restrict__ L, const T* __rest
             for (int e = 0; e < w; ++e) acc[e] = wr * ldf(O + row * d + c + e);
         }
         for (int s = 0; s < n; ++s) {
-            const float ws = mx == -INFINITY ? 0.f : expf(Lp[s * l_stride + row] - mx) * inv;
+            const float ws = mx == -INFINITY ? 0.f : expf(lse_of(s) - mx) * inv;
+            if (ws == 0.f) continue;                                    // (also keeps stale bits of uncovered rows out)
             const T* src = Op + s * o_stride + row * d + c;
             if (w == 4 && (d & 3) == 0) {
                 if constexpr (sizeof(T) == 2) {
@@ -471,15 +476,18 @@ int lse_merge(void* Oa, float* La, const void* Ob, const float* Lb, size_t rows,
 }
 
 int lse_merge_multi(void* O, float* L, const void* Op, const float* Lp, size_t o_stride, size_t l_stride, int n, bool running,
-                    size_t rows, int d, int dtype, cudaStream_t st)
+                    size_t rows, int d, int dtype, cudaStream_t st, int Nl, int c, unsigned upper_mask)
 {
+    if (n > 32) return B200_ERR_UNSUPPORTED;
+    if (Nl <= 0) { Nl = 1; upper_mask = 0u; }
     if (rows == 0 || (n == 0 && running)) return B200_OK;
     unsigned grid = (unsigned)((rows + 7) / 8);
     if (dtype == B200_DTYPE_F32)
-        lse_merge_multi_kernel<float><<<grid, 256, 0, st>>>((float*)O, L, (const float*)Op, Lp, o_stride, l_stride, n, running ? 1 : 0, rows, d);
+        lse_merge_multi_kernel<float><<<grid, 256, 0, st>>>((float*)O, L, (const float*)Op, Lp, o_stride, l_stride, n, running ? 1 : 0, rows, d,
+                                                                Nl, c, upper_mask);
     else
         lse_merge_multi_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((__nv_bfloat16*)O, L, (const __nv_bfloat16*)Op, Lp, o_stride, l_stride, n,
-                                                                     running ? 1 : 0, rows, d);
+                                                                     running ? 1 : 0, rows, d, Nl, c, upper_mask);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;

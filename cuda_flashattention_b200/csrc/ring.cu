@@ -353,16 +353,36 @@ int b200_ring_exchange_kv(const void* send_k, void* recv_k, const void* send_v, 
     return exchange(s, r, b, 2, next_rank, prev_rank, comm, st);
 }
 
-int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nl, int d,
-                  float scale, int dtype, ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+}  // extern "C"
+
+// Causal ring (B200_FLAG_CAUSAL): ZIGZAG sharding.  The sequence is cut into 2P chunks of c = Nl/2 rows and rank r
+// holds chunk r (local rows [0,c)) followed by chunk 2P-1-r (rows [c,2c)) -- the load-balanced placement the
+// reference's notes ask for (__info__/README.md:173).  With that placement every ring step is a plain rectangle:
+//   step 0 (own block)            : causal attention on the local 2c x 2c problem;
+//   block from a rank b < r       : ALL local queries against the FIRST half of the block (chunk b precedes both
+//                                   local chunks, chunk 2P-1-b follows both);
+//   block from a rank b > r       : the SECOND half of the local queries against ALL of the block.
+// Each step is 2c^2 score pairs on every rank -- no rank idles -- and needs no mask beyond step 0; the halves are
+// row sub-blocks of the same buffers, addressed through the strided forward.
+static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nl, int d,
+                         float scale, int dtype, int flags, ncclComm_t comm, int rank, int nranks, cudaStream_t st)
 {
     if (nranks <= 0 || rank < 0 || rank >= nranks || B < 0 || H < 0 || Nl < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (dtype != B200_DTYPE_BF16 && dtype != B200_DTYPE_F32) return B200_ERR_INVALID_ARGUMENT;
+    if ((flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
     if ((size_t)B * H * Nl == 0) return B200_OK;
     if (!Q || !K || !V || !O || !L) return B200_ERR_INVALID_ARGUMENT;     // the merge needs the LSE
-    if (nranks == 1) return b200_fa2_fwd(Q, K, V, O, L, B, H, Nl, Nl, d, scale, dtype, st);
+    if (nranks == 1) return b200_fa2_fwd_ex(Q, K, V, O, L, B, H, Nl, Nl, d, scale, dtype, flags, st);
     if (!comm) return B200_ERR_INVALID_ARGUMENT;
     B200_TRY(device_check());
+    const int c = Nl / 2;
+    if (causal) {
+        if ((Nl & 1) || nranks > 32) return B200_ERR_INVALID_ARGUMENT;
+        const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
+        if (!b200_fwd_uses_tensor_cores(dtype, d, c, c) || (al & 15) || B > 65535 || H > 65535) return B200_ERR_UNSUPPORTED;
+        if (!(scale > 0.0f)) scale = 1.0f / sqrtf((float)d);
+    }
 
     RingState* rs;
     B200_TRY(ring_state(&rs));
@@ -393,7 +413,10 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
     float* Lpart = reinterpret_cast<float*>(p + align256(kv_bytes));
     auto Opb = [&](int i) { return (void*)(Opart + (size_t)i * part_bytes); };
     auto Lpb = [&](int i) { return reinterpret_cast<float*>(Opart + (size_t)i * part_bytes + align256(kv_bytes)); };
-    if (!ce) NB = 2;
+    const bool deferred = ce || causal;       // one partial per step + n-way merge (the NCCL non-causal path keeps pairwise merges)
+    if (!deferred) NB = 2;
+    unsigned upper_mask = 0u;                 // causal: partials of the current group that only cover the rows >= c
+    const Lay lay = lay_contiguous(H, Nl, d);
 
     const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
     // the side streams may start once everything already enqueued on the caller's stream is done
@@ -411,7 +434,7 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
         // copy-engine mode: the attention of consecutive steps runs on two alternating streams (the merges stay
         // on the caller's stream), so a step's last, partly filled wave overlaps the next step's first one
         cudaStream_t as = ce ? rs->attn_stream[step & 1] : st;
-        const int pb = ce ? step % NB : (step & 1);
+        const int pb = deferred ? step % NB : (step & 1);
         void* Op = Opb(pb); float* Lp = Lpb(pb);
         if (ce && step >= 1) {
             // the block of this step was pushed into cur_slot by the previous rank: both streams wait for it
@@ -433,17 +456,34 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
             }
         }
         // attention of the local queries against the current block (overlaps the exchange above)
-        if (ce) {
+        if (deferred) {
             // (only when the partials did not all fit) the group merge that consumed this buffer must be done
-            if (step >= NB) B200_CUDA_TRY(cudaStreamWaitEvent(as, rs->ev_merge[0], 0));
-            B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
-            B200_CUDA_TRY(cudaEventRecord(rs->ev_attn[step & 1], as));
-            B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_attn[step & 1], 0));
+            if (ce && step >= NB) B200_CUDA_TRY(cudaStreamWaitEvent(as, rs->ev_merge[0], 0));
+            const int blk = (rank - step + nranks) % nranks;
+            if (!causal) {
+                B200_TRY(b200_fa2_fwd(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, as));
+            } else if (step == 0) {
+                B200_TRY(b200_fa2_fwd_ex(Q, Kc, Vc, Op, Lp, B, H, Nl, Nl, d, scale, dtype, B200_FLAG_CAUSAL, as));
+            } else if (blk < rank) {
+                FwdArgs a{Q, Kc, Vc, Op, Lp, lay, lay, lay, lay, (long long)Nl, B, H, H, Nl, c, d, scale, dtype, false};
+                B200_TRY(tc_fwd_strided(a, as));
+            } else {
+                const size_t ro = (size_t)c * d * es;              // byte offset of local row c
+                FwdArgs a{(const uint8_t*)Q + ro, Kc, Vc, (uint8_t*)Op + ro, Lp + c, lay, lay, lay, lay, (long long)Nl,
+                          B, H, H, c, Nl, d, scale, dtype, false};
+                B200_TRY(tc_fwd_strided(a, as));
+                upper_mask |= 1u << pb;
+            }
+            if (ce) {
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_attn[step & 1], as));
+                B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_attn[step & 1], 0));
+            }
             if (pb == NB - 1 || step == nranks - 1) {
                 // fold partials 0 .. pb (and, after the first group, the running result) into (O, L)
                 B200_TRY(lse_merge_multi(O, L, Opart, Lpart, part_bytes / es, part_bytes / sizeof(float), pb + 1, step >= NB,
-                                         (size_t)B * H * Nl, d, dtype, st));
-                B200_CUDA_TRY(cudaEventRecord(rs->ev_merge[0], st));
+                                         (size_t)B * H * Nl, d, dtype, st, Nl, c, upper_mask));
+                upper_mask = 0u;
+                if (ce) B200_CUDA_TRY(cudaEventRecord(rs->ev_merge[0], st));
             }
         } else {
             if (step == 0) B200_TRY(b200_fa2_fwd(Q, Kc, Vc, O, L, B, H, Nl, Nl, d, scale, dtype, as));
@@ -469,6 +509,26 @@ int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L
         B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
     }
     return B200_OK;
+}
+
+extern "C" {
+
+int b200_ring_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nl, int d,
+                  float scale, int dtype, ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+{
+    return ring_fwd_impl(Q, K, V, O, L, B, H, Nl, d, scale, dtype, 0, comm, rank, nranks, st);
+}
+
+int b200_ring_zigzag_chunk(int rank, int half, int nranks)
+{
+    if (nranks <= 0 || rank < 0 || rank >= nranks || (half != 0 && half != 1)) return -1;
+    return half == 0 ? rank : 2 * nranks - 1 - rank;
+}
+
+int b200_ring_fwd_ex(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nl, int d,
+                     float scale, int dtype, int flags, ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+{
+    return ring_fwd_impl(Q, K, V, O, L, B, H, Nl, d, scale, dtype, flags, comm, rank, nranks, st);
 }
 
 int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,

@@ -37,16 +37,25 @@ def ring_kv_block(rank, step, nranks):
     return lib.b200_ring_kv_block(rank, step, nranks)
 
 
-def ring_attention_forward(Q_local, K_local, V_local, comm, softmax_scale=0.0):
-    """-> (O_local, L_local).  K_local/V_local are left untouched (the reference overwrites them)."""
+def zigzag_rows(rank, nranks, n_total):
+    """Global row indices that rank `rank` holds under the zigzag sharding of the causal ring: chunk `rank` followed by
+    chunk `2P-1-rank` of the 2P chunks of n_total/(2P) rows."""
+    c = n_total // (2 * nranks)
+    lo, hi = lib.b200_ring_zigzag_chunk(rank, 0, nranks), lib.b200_ring_zigzag_chunk(rank, 1, nranks)
+    return list(range(lo * c, (lo + 1) * c)) + list(range(hi * c, (hi + 1) * c))
+
+
+def ring_attention_forward(Q_local, K_local, V_local, comm, softmax_scale=0.0, causal=False):
+    """-> (O_local, L_local).  K_local/V_local are left untouched (the reference overwrites them).
+    causal=True expects the zigzag sharding (zigzag_rows)."""
     _check_inputs(Q_local, K_local, V_local)
     B, H, Nl, d = _bhnd(Q_local)
     O = torch.empty_like(Q_local)
     L = torch.empty(Q_local.shape[:-1], dtype=torch.float32, device=Q_local.device)
     with torch.cuda.device(Q_local.device):
-        check(lib.b200_ring_fwd(Q_local.data_ptr(), K_local.data_ptr(), V_local.data_ptr(), O.data_ptr(), L.data_ptr(),
-                                B, H, Nl, d, float(softmax_scale), _dtype_code(Q_local),
-                                comm.handle, comm.rank, comm.nranks, _stream()), "b200_ring_fwd")
+        check(lib.b200_ring_fwd_ex(Q_local.data_ptr(), K_local.data_ptr(), V_local.data_ptr(), O.data_ptr(), L.data_ptr(),
+                                   B, H, Nl, d, float(softmax_scale), _dtype_code(Q_local), 1 if causal else 0,
+                                   comm.handle, comm.rank, comm.nranks, _stream()), "b200_ring_fwd_ex")
     return O, L
 
 

@@ -195,6 +195,18 @@ B200_API int b200_ring_bwd(const void* Q_local, const void* K_local, const void*
                   int B, int H, int N_local, int d, float scale, int dtype,
                   ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
 
+/* Causal ring forward (flags = B200_FLAG_CAUSAL; flags = 0 is b200_ring_fwd).  ZIGZAG sharding: the sequence of
+ * P*N_local rows is cut into 2P chunks of N_local/2 rows and rank r holds chunk r followed by chunk 2P-1-r
+ * (b200_ring_zigzag_chunk gives the two chunk indices), which gives every rank the same work under the causal mask --
+ * the load-balanced placement the reference's notes list as future work (__info__/README.md:173).  Every step after
+ * the first is an unmasked rectangle (all local queries x the first half of the visiting block, or the second half of
+ * the local queries x the whole block).  Needs the tensor-core shapes (d in {64,128}), N_local even, P <= 32. */
+B200_API int b200_ring_fwd_ex(const void* Q_local, const void* K_local, const void* V_local, void* O_local, float* L_local,
+                     int B, int H, int N_local, int d, float scale, int dtype, int flags,
+                     ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
+/* chunk index (0 .. 2P-1) held in half `half` (0 / 1) of rank `rank`'s local rows under the zigzag sharding */
+B200_API int b200_ring_zigzag_chunk(int rank, int half, int nranks);
+
 /* NCCL bootstrap without MPI (replaces init_nccl_comm / cleanup_mpi_nccl, src/util/nccl_utils.h:29-103):
  * rank 0 calls b200_ring_unique_id and ships the 128 bytes to the other ranks by any means
  * (file, env, torch.distributed store), then every rank calls b200_ring_comm_init. */

@@ -55,3 +55,31 @@ def test_no_cpu_fallback():
     q = torch.zeros(4, 4)
     with pytest.raises(ValueError):
         fa.flash_attention_2_forward(q, q, q)
+
+
+def test_zigzag_causal_ring_schedule_covers_the_causal_triangle_evenly():
+    # host logic of b200_ring_fwd_ex(B200_FLAG_CAUSAL): step 0 = local causal; a block from rank b < r = all local
+    # queries x first half of the block; from b > r = second half of the local queries x the whole block.
+    # Check on chunk granularity that the rectangles are exactly the visible pairs, once each, same area every step.
+    for P in (1, 2, 3, 4, 8):
+        for r in range(P):
+            mine = [fa.lib.b200_ring_zigzag_chunk(r, 0, P), fa.lib.b200_ring_zigzag_chunk(r, 1, P)]
+            assert mine == [r, 2 * P - 1 - r]
+            seen = set()
+            for s in range(P):
+                b = fa.ring_kv_block(r, s, P)
+                theirs = [b, 2 * P - 1 - b]
+                if s == 0:
+                    pairs = {(mine[0], mine[0], "diag"), (mine[1], mine[0], "full"), (mine[1], mine[1], "diag")}
+                elif b < r:
+                    pairs = {(mine[0], theirs[0], "full"), (mine[1], theirs[0], "full")}
+                else:
+                    pairs = {(mine[1], theirs[0], "full"), (mine[1], theirs[1], "full")}
+                area = sum(1.0 if kind == "full" else 0.5 for _, _, kind in pairs)
+                assert area == 2.0                                   # every step costs the same on every rank
+                for q, k, kind in pairs:
+                    assert (k < q and kind == "full") or (k == q and kind == "diag")
+                    assert (q, k) not in seen
+                    seen.add((q, k))
+            want = {(q, k) for q in mine for k in range(2 * P) if k <= q}
+            assert seen == want
