@@ -64,6 +64,7 @@ _SIGS = {
     "b200_ring_kv_block": (_i, [_i, _i, _i]),
     "b200_ring_fwd": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
     "b200_ring_fwd_ex": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
+    "b200_ring_bwd_ex": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
     "b200_ring_zigzag_chunk": (_i, [_i, _i, _i]),
     "b200_ring_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
     "b200_ring_unique_id": (_i, [_vp]),

@@ -158,8 +158,8 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
 // instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
 template <int DR>
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
-                                               float* __restrict__ dQacc, int Nq, int n_tot, int n_it, int qt_min, int i_off,
-                                               size_t bhq0, int dbg)
+                                               float* __restrict__ dQacc, int Nq, int dq_rows, int n_tot, int n_it, int qt_min,
+                                               int i_off, size_t bhq0, int dbg)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
@@ -182,7 +182,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         __syncwarp();
         if (lane0) mbar_arrive(bar_dQ_empty);                          // TMEM columns are free again
         B200_TRB(1, i, 1);
-        float* dst = dQacc + (bh * Nq + (size_t)qt * BM) * DR + r;
+        float* dst = dQacc + (bh * dq_rows + (size_t)qt * BM) * DR + r;   // (dq_rows: rows per slab of the accumulator)
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
         if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
             if (q_valid == BM) {
@@ -240,7 +240,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
            float* __restrict__ dQacc, const __grid_constant__ CUtensorMap tmdK,
            const __grid_constant__ CUtensorMap tmdV, const float* __restrict__ L2p, const float* __restrict__ Dp,
-           int Nq, int Nq_pad, float scale_log2, float scale, int dbg, int causal, int G, int BHkv)
+           int Nq, int stat_stride, int dq_rows, float scale_log2, float scale, int dbg, int causal, int G, int BHkv)
 {
     using namespace bwd;
     extern __shared__ uint8_t smem_raw[];
@@ -311,8 +311,8 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 if (qt >= n_it) qt -= n_it;
                 qt += qt_min;
                 const int h = hk * G + g;
-                const float* Lrow = L2p + (bhq0 + g) * Nq_pad;
-                const float* Drow = Dp + (bhq0 + g) * Nq_pad;
+                const float* Lrow = L2p + (bhq0 + g) * stat_stride;
+                const float* Drow = Dp + (bhq0 + g) * stat_stride;
                 if (++ii == n_it) { ii = 0; ++g; }
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
                 mbar_expect_tx(&bar_in_full[s], 2 * NBOX * Q_BOX + 2 * STAT_BYTES);
@@ -394,7 +394,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         tc_fence_after();
         bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, hk, b);
     } else if (warp >= 12) {
-        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, n_tot, n_it, qt_min, i_off, bhq0, dbg);
+        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, dq_rows, n_tot, n_it, qt_min, i_off, bhq0, dbg);
     }
 
     tc_fence_before();
@@ -480,6 +480,7 @@ struct BwdLaunch {
     Lay lq, lk, lv, ldo, ldk, ldv;
     int Bm, Hkv, G, BHkv;            // grid / map batches and K/V heads, group size, valid K/V slabs (<= Bm * Hkv)
     int Nq, Nkv; float scale; bool causal;
+    int stat_stride = 0, dq_rows = 0;    // floats per slab of L2p / Dp and rows per slab of dQacc; 0 = pad64(Nq) / Nq
 };
 
 template <int DR>
@@ -504,7 +505,8 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     dim3 grid((a.Nkv + BN - 1) / BN, a.Hkv, a.Bm);
     static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
     if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
-    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq, Nq_pad,
+    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
+                                                a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
                                                 a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
@@ -607,10 +609,27 @@ int tc_bwd_ring_prepare(const float* L, const float* Dvec, void* stats, int BH, 
 int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
                      float* dQacc, void* dKp, void* dVp, int BH, int Nq, int Nkv, float scale, cudaStream_t st)
 {
-    const int Nq_pad = (Nq + 63) / 64 * 64;
+    return tc_bwd_ring_step_sub(Q, K, V, dO, stats, dQacc, dKp, dVp, BH, Nq, 0, Nq, Nkv, false, scale, st);
+}
+
+// The same on a row sub-block (causal zigzag ring): queries q_row0 .. q_row0 + Nq - 1 of every Nl-row slab against the
+// first Nkv rows of the visiting block; all buffers keep their Nl-row slabs.  Only rows [0, Nkv) of dKp / dVp are written.
+int tc_bwd_ring_step_sub(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
+                         float* dQacc, void* dKp, void* dVp, int BH, int Nl, int q_row0, int Nq, int Nkv, bool causal,
+                         float scale, cudaStream_t st)
+{
+    const int Nl_pad = (Nl + 63) / 64 * 64;
     const float* L2p = reinterpret_cast<const float*>(stats);
-    const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
-    const BwdLaunch a = contiguous_launch(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, BH, Nq, Nkv, 128, scale, false);
+    const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nl_pad * sizeof(float)));
+    if (q_row0 != 0 && (q_row0 % 64 != 0)) return B200_ERR_UNSUPPORTED;     // statistics tiles must stay inside the slab's padding
+    const size_t qo = (size_t)q_row0 * 128;
+    BwdLaunch a = contiguous_launch(reinterpret_cast<const __nv_bfloat16*>(Q) + qo, K, V, reinterpret_cast<const __nv_bfloat16*>(dO) + qo,
+                                    L2p + q_row0, Dp + q_row0, dQacc + qo, dKp, dVp, BH, Nq, Nkv, 128, scale, causal);
+    // slabs are Nl rows apart whatever the sub-block covers
+    const Lay full = lay_contiguous(a.Hkv, Nl, 128);
+    a.lq = a.ldo = a.lk = a.lv = a.ldk = a.ldv = full;
+    a.stat_stride = Nl_pad;
+    a.dq_rows = Nl;
     return bwd_launch<128>(a, st);
 }
 

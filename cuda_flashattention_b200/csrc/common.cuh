@@ -84,6 +84,9 @@ size_t tc_bwd_ring_stats_bytes(int BH, int Nq);
 int tc_bwd_ring_prepare(const float* L, const float* D, void* stats, int BH, int Nq, cudaStream_t st);
 int tc_bwd_ring_step(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
                      float* dQacc, void* dKp, void* dVp, int BH, int Nq, int Nkv, float scale, cudaStream_t st);
+int tc_bwd_ring_step_sub(const void* Q, const void* K, const void* V, const void* dO, const void* stats,
+                         float* dQacc, void* dKp, void* dVp, int BH, int Nl, int q_row0, int Nq, int Nkv, bool causal,
+                         float scale, cudaStream_t st);
 
 // ---- per-device scratch arena (api.cu) ------------------------------------------------------------
 // Grows monotonically; reuse across calls is safe because all users are stream-ordered on the

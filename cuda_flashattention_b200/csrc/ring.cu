@@ -257,6 +257,27 @@ __global__ void __launch_bounds__(256) accum_kernel(float* __restrict__ acc, con
         }
     }
 }
+// the same for the first `nrows` rows of every slab of `slab_rows` rows of d elements (d % 4 == 0): causal ring steps
+// that only produced gradients for the first half of the visiting K/V block
+template <typename T>
+__global__ void __launch_bounds__(256) accum_rows_kernel(float* __restrict__ acc, const T* __restrict__ part, size_t slabs,
+                                                         int slab_rows, int nrows, int d)
+{
+    const size_t per = (size_t)nrows * d / 4;
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= slabs * per) return;
+    const size_t slab = idx / per, i = slab * (size_t)slab_rows * d + (idx - slab * per) * 4;
+    float4 a = *reinterpret_cast<float4*>(acc + i);
+    if constexpr (sizeof(T) == 4) {
+        const float4 p = *reinterpret_cast<const float4*>(part + i);
+        a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+    } else {
+        uint2 raw = *reinterpret_cast<const uint2*>(part + i);
+        __nv_bfloat162 lo = *reinterpret_cast<__nv_bfloat162*>(&raw.x), hi = *reinterpret_cast<__nv_bfloat162*>(&raw.y);
+        a.x += __low2float(lo); a.y += __high2float(lo); a.z += __low2float(hi); a.w += __high2float(hi);
+    }
+    *reinterpret_cast<float4*>(acc + i) = a;
+}
 // out[i] = (T)acc[i]
 template <typename T>
 __global__ void __launch_bounds__(256) cast_kernel(T* __restrict__ out, const float* __restrict__ acc, size_t n)
@@ -272,6 +293,16 @@ static int accum(float* acc, const void* part, size_t n, int dtype, cudaStream_t
     unsigned grid = (unsigned)((n / 4 + 255) / 256 + 1);
     if (dtype == B200_DTYPE_F32) accum_kernel<float><<<grid, 256, 0, st>>>(acc, (const float*)part, n);
     else accum_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(acc, (const __nv_bfloat16*)part, n);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+static int accum_rows(float* acc, const void* part, size_t slabs, int slab_rows, int nrows, int d, int dtype, cudaStream_t st)
+{
+    const size_t n4 = slabs * (size_t)nrows * d / 4;
+    const unsigned grid = (unsigned)((n4 + 255) / 256);
+    if (dtype == B200_DTYPE_F32) accum_rows_kernel<float><<<grid, 256, 0, st>>>(acc, (const float*)part, slabs, slab_rows, nrows, d);
+    else accum_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(acc, (const __nv_bfloat16*)part, slabs, slab_rows, nrows, d);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
@@ -531,17 +562,29 @@ int b200_ring_fwd_ex(const void* Q, const void* K, const void* V, void* O, float
     return ring_fwd_impl(Q, K, V, O, L, B, H, Nl, d, scale, dtype, flags, comm, rank, nranks, st);
 }
 
-int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
-                  void* dQ, void* dK, void* dV, int B, int H, int Nl, int d, float scale, int dtype,
-                  ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+}  // extern "C"
+
+// Causal (zigzag) ring backward: the rectangles of ring_fwd_impl, with the dK/dV partial of a "first half of the
+// block" step added into the first half of the travelling accumulators only.
+static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                         void* dQ, void* dK, void* dV, int B, int H, int Nl, int d, float scale, int dtype, int flags,
+                         ncclComm_t comm, int rank, int nranks, cudaStream_t st)
 {
     if (nranks <= 0 || rank < 0 || rank >= nranks || B < 0 || H < 0 || Nl < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (dtype != B200_DTYPE_BF16 && dtype != B200_DTYPE_F32) return B200_ERR_INVALID_ARGUMENT;
+    if ((flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
     if ((size_t)B * H * Nl == 0) return B200_OK;
     if (!Q || !K || !V || !O || !L || !dO || !dQ || !dK || !dV) return B200_ERR_INVALID_ARGUMENT;
-    if (nranks == 1) return b200_fa2_bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st);
+    if (nranks == 1) return b200_fa2_bwd_ex(Q, K, V, O, L, dO, dQ, dK, dV, B, H, Nl, Nl, d, scale, dtype, flags, nullptr, 0, st);
     if (!comm) return B200_ERR_INVALID_ARGUMENT;
     B200_TRY(device_check());
+    const int c = Nl / 2;
+    if (causal) {
+        // needs the tensor-core step kernel (bf16, d = 128) and half-blocks that are whole 64-row statistics tiles
+        if (!(tc_bwd_ring_supported(dtype, d, B * H, Q, K, V, dO) && b200_bwd_uses_tensor_cores(dtype, d, Nl, Nl)) || Nl % 128 != 0)
+            return B200_ERR_UNSUPPORTED;
+    }
 
     RingState* rs;
     B200_TRY(ring_state(&rs));
@@ -614,8 +657,14 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
                 B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[slot], rs->comm_stream));
             }
         }
+        const int blk = (rank - step + nranks) % nranks;
+        const bool first_half_only = causal && step > 0 && blk < rank;   // dK/dV of this step exist for rows [0, c) only
         if (fused) {
-            B200_TRY(tc_bwd_ring_step(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, Nl, scale == 0.0f ? 1.0f / sqrtf((float)d) : scale, st));
+            const float sc = scale == 0.0f ? 1.0f / sqrtf((float)d) : scale;
+            if (!causal) B200_TRY(tc_bwd_ring_step(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, Nl, sc, st));
+            else if (step == 0) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, Nl, true, sc, st));
+            else if (blk < rank) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, c, false, sc, st));
+            else B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, c, c, Nl, false, sc, st));
         } else {
             B200_TRY(b200_fa2_bwd(Q, Kc, Vc, O, L, dO, dQp, dKp, dVp, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st));
             B200_TRY(accum(dQa, dQp, n_el, dtype, st));
@@ -625,8 +674,13 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
             if (ce) B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
             else B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
         }
-        B200_TRY(accum(dKa[cur], dKp, n_el, dtype, st));
-        B200_TRY(accum(dVa[cur], dVp, n_el, dtype, st));
+        if (first_half_only) {
+            B200_TRY(accum_rows(dKa[cur], dKp, (size_t)B * H, Nl, c, d, dtype, st));
+            B200_TRY(accum_rows(dVa[cur], dVp, (size_t)B * H, Nl, c, d, dtype, st));
+        } else {
+            B200_TRY(accum(dKa[cur], dKp, n_el, dtype, st));
+            B200_TRY(accum(dVa[cur], dVp, n_el, dtype, st));
+        }
         // hand the accumulators to the next rank (queued behind this step's K/V prefetch)
         B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
         B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
@@ -666,6 +720,22 @@ int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, co
     B200_TRY(cast_out(dK, dKa[cur], n_el, dtype, st));
     B200_TRY(cast_out(dV, dVa[cur], n_el, dtype, st));
     return B200_OK;
+}
+
+extern "C" {
+
+int b200_ring_bwd(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                  void* dQ, void* dK, void* dV, int B, int H, int Nl, int d, float scale, int dtype,
+                  ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+{
+    return ring_bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, B, H, Nl, d, scale, dtype, 0, comm, rank, nranks, st);
+}
+
+int b200_ring_bwd_ex(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                     void* dQ, void* dK, void* dV, int B, int H, int Nl, int d, float scale, int dtype, int flags,
+                     ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+{
+    return ring_bwd_impl(Q, K, V, O, L, dO, dQ, dK, dV, B, H, Nl, d, scale, dtype, flags, comm, rank, nranks, st);
 }
 
 }  // extern "C"

@@ -59,13 +59,13 @@ def ring_attention_forward(Q_local, K_local, V_local, comm, softmax_scale=0.0, c
     return O, L
 
 
-def ring_attention_backward(Q_local, K_local, V_local, O_local, L_local, dO_local, comm, softmax_scale=0.0):
+def ring_attention_backward(Q_local, K_local, V_local, O_local, L_local, dO_local, comm, softmax_scale=0.0, causal=False):
     _check_inputs(Q_local, K_local, V_local, O_local, dO_local)
     B, H, Nl, d = _bhnd(Q_local)
     dQ, dK, dV = torch.empty_like(Q_local), torch.empty_like(K_local), torch.empty_like(V_local)
     with torch.cuda.device(Q_local.device):
-        check(lib.b200_ring_bwd(Q_local.data_ptr(), K_local.data_ptr(), V_local.data_ptr(), O_local.data_ptr(),
-                                L_local.data_ptr(), dO_local.data_ptr(), dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(),
-                                B, H, Nl, d, float(softmax_scale), _dtype_code(Q_local),
-                                comm.handle, comm.rank, comm.nranks, _stream()), "b200_ring_bwd")
+        check(lib.b200_ring_bwd_ex(Q_local.data_ptr(), K_local.data_ptr(), V_local.data_ptr(), O_local.data_ptr(),
+                                   L_local.data_ptr(), dO_local.data_ptr(), dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(),
+                                   B, H, Nl, d, float(softmax_scale), _dtype_code(Q_local), 1 if causal else 0,
+                                   comm.handle, comm.rank, comm.nranks, _stream()), "b200_ring_bwd_ex")
     return dQ, dK, dV

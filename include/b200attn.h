@@ -204,6 +204,11 @@ B200_API int b200_ring_bwd(const void* Q_local, const void* K_local, const void*
 B200_API int b200_ring_fwd_ex(const void* Q_local, const void* K_local, const void* V_local, void* O_local, float* L_local,
                      int B, int H, int N_local, int d, float scale, int dtype, int flags,
                      ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
+/* Causal ring backward on the same zigzag sharding (bf16, d = 128, N_local a multiple of 128). */
+B200_API int b200_ring_bwd_ex(const void* Q_local, const void* K_local, const void* V_local, const void* O_local,
+                     const float* L_local, const void* dO_local, void* dQ_local, void* dK_local, void* dV_local,
+                     int B, int H, int N_local, int d, float scale, int dtype, int flags,
+                     ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
 /* chunk index (0 .. 2P-1) held in half `half` (0 / 1) of rank `rank`'s local rows under the zigzag sharding */
 B200_API int b200_ring_zigzag_chunk(int rank, int half, int nranks);
 

@@ -47,17 +47,22 @@ def main():
     # ---- causal ring forward, zigzag sharding (extension): every rank holds chunk r and chunk 2P-1-r
     for (dtype, H, N, d, tol) in ((torch.bfloat16, 2, 256 * world, 128, 2e-2), (torch.float32, 1, 384 * world, 64, 2e-3)):
         rng = np.random.default_rng(11)
-        Q, K, V = [rng.standard_normal((1, H, N, d)).astype(np.float32) for _ in range(3)]
+        Q, K, V, dO = [rng.standard_normal((1, H, N, d)).astype(np.float32) for _ in range(4)]
         rows = fa.zigzag_rows(rank, world, N)
         to = lambda a: torch.from_numpy(a[:, :, rows].copy()).cuda().to(dtype).contiguous()
-        q, k, v = to(Q), to(K), to(V)
+        q, k, v, do = to(Q), to(K), to(V), to(dO)
         O, L = fa.ring_attention_forward(q, k, v, comm, 0.0, causal=True)
+        grads = fa.ring_attention_backward(q, k, v, O, L, do, comm, 0.0, causal=True) if dtype == torch.bfloat16 else None
         torch.cuda.synchronize()
         rt = lambda a: torch.from_numpy(a).cuda().to(dtype).float().cpu().numpy()      # what the GPUs saw
         for h in range(H):
             Oo, Lo = oracle.forward(rt(Q[0, h]), rt(K[0, h]), rt(V[0, h]), 0.0, causal=True)
             scl = max(1.0, float(np.abs(Oo).max()))
             errs = {"O": np.abs(O[0, h].float().cpu().numpy() - Oo[rows]).max() / scl, "L": np.abs(L[0, h].cpu().numpy() - Lo[rows]).max()}
+            if grads is not None:
+                ref = oracle.backward(rt(Q[0, h]), rt(K[0, h]), rt(V[0, h]), rt(dO[0, h]), 0.0, causal=True)
+                for name, got, want in zip(("dQ", "dK", "dV"), grads, ref):
+                    errs[name] = np.abs(got[0, h].float().cpu().numpy() - want[rows]).max() / max(1.0, float(np.abs(want).max()))
             if rank == 0:
                 print("causal zigzag", dtype, "head", h, {k_: float(v_) for k_, v_ in errs.items()})
             ok = ok and all(e <= tol for e in errs.values())
