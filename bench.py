@@ -31,6 +31,7 @@ UNIT = "TFLOP/s"
 B0, H0, N0, D0 = 8, 16, 8192, 128
 
 
+CAUSAL = False                # --causal: the causal extension (zigzag-sharded ring at N > 1); FLOPs counted on the visible half
 WORKLOAD = "default"          # --workload c5: BASELINE.json configs[4] (B=1 H=32 N=262144 d=128) sharded over the ranks
 
 
@@ -54,6 +55,8 @@ def config_dict(n_gpus):
                 "l2_policy": "inputs larger than L2"}
     name = ("C3 FA2 fwd+bwd B=8 H=16 N=8192 d=128 bf16" if n_gpus == 1 else
             f"ring fwd+bwd B={B} H={H} N={Nt} d={d} bf16 over {n_gpus} GPUs (N_local={Nl}; C4 shape at 8 GPUs)")
+    if CAUSAL:
+        name += " CAUSAL (extension; zigzag-sharded ring; FLOPs of the visible half)"
     return {"workload": name, "B": B, "H": H, "N_total": Nt, "N_local": Nl, "d": d,
             "parallelism": "single" if n_gpus == 1 else f"ring-sp{n_gpus}",
             "l2_policy": "inputs larger than L2 (4 x 268 MB bf16 tensors vs 126 MB L2)"}
@@ -224,17 +227,19 @@ def run_ours(args):
     P = lambda t: t.data_ptr()
     ch = comm.handle if comm else None
 
+    FL = 1 if CAUSAL else 0          # B200_FLAG_CAUSAL; flags = 0 is exactly b200_fa2_fwd / b200_ring_fwd
+
     def fwd():
         if world == 1:
-            check(lib.b200_fa2_fwd(P(q), P(k), P(v), P(O), P(L), B, H, Nl, Nl, d, 0.0, 0, st), "fwd")
+            check(lib.b200_fa2_fwd_ex(P(q), P(k), P(v), P(O), P(L), B, H, Nl, Nl, d, 0.0, 0, FL, st), "fwd")
         else:
-            check(lib.b200_ring_fwd(P(q), P(k), P(v), P(O), P(L), B, H, Nl, d, 0.0, 0, ch, rank, world, st), "ring_fwd")
+            check(lib.b200_ring_fwd_ex(P(q), P(k), P(v), P(O), P(L), B, H, Nl, d, 0.0, 0, FL, ch, rank, world, st), "ring_fwd")
 
     def bwd():
         if world == 1:
-            check(lib.b200_fa2_bwd(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, Nl, d, 0.0, 0, None, 0, st), "bwd")
+            check(lib.b200_fa2_bwd_ex(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, Nl, d, 0.0, 0, FL, None, 0, st), "bwd")
         else:
-            check(lib.b200_ring_bwd(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, d, 0.0, 0, ch, rank, world, st), "ring_bwd")
+            check(lib.b200_ring_bwd_ex(P(q), P(k), P(v), P(O), P(L), P(dO), P(dQ), P(dK), P(dV), B, H, Nl, d, 0.0, 0, FL, ch, rank, world, st), "ring_bwd")
 
     def barrier():
         if world > 1:
@@ -264,6 +269,8 @@ def run_ours(args):
     total_ms, fwd_ms, bwd_ms = [float(x) for x in t.tolist()]
     ms_per_step = total_ms / args.steps
     flops_rank = 14.0 * B * H * Nl * Nt * d
+    if CAUSAL:                       # visible pairs only: Nt (Nt + 1) / 2 over the whole job, the same on every rank (zigzag)
+        flops_rank = 14.0 * B * H * (Nt * (Nt + 1.0) / 2.0) / world * d
     value = world * flops_rank / (ms_per_step * 1e-3) / 1e12
 
     # ---- end to end: host (pinned) buffers in, host buffers out, copies inside the timed region
@@ -315,15 +322,16 @@ def run_ours(args):
         pk = peaks()
         tc_bwd = bool(lib.b200_bwd_uses_tensor_cores(0, d, Nl, Nl))
         dom = "bwd" if bwd_ms >= fwd_ms else "fwd"
-        dom_flops = (10.0 if dom == "bwd" else 4.0) * B * H * Nl * Nt * d
+        pairs = flops_rank / 14.0 / d               # score pairs per rank (B*H*Nl*Nt, or the visible half when causal)
+        dom_flops = (10.0 if dom == "bwd" else 4.0) * pairs * d
         dom_ms = bwd_ms if dom == "bwd" else fwd_ms
         achieved = dom_flops / (dom_ms * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic", "config": config_dict(world),
-            "fwd": {"ms": fwd_ms, "tflops_per_gpu": 4.0 * B * H * Nl * Nt * d / (fwd_ms * 1e-3) / 1e12},
-            "bwd": {"ms": bwd_ms, "tflops_per_gpu": 10.0 * B * H * Nl * Nt * d / (bwd_ms * 1e-3) / 1e12,
+            "fwd": {"ms": fwd_ms, "tflops_per_gpu": 4.0 * pairs * d / (fwd_ms * 1e-3) / 1e12},
+            "bwd": {"ms": bwd_ms, "tflops_per_gpu": 10.0 * pairs * d / (bwd_ms * 1e-3) / 1e12,
                     "kernel_family": "tcgen05" if tc_bwd else "generic CUDA-core (tcgen05 backward not built yet)"},
             "pct_of_nominal_2250": 100.0 * value / world / 2250.0,
             "roofline": {"bound": "tensor", "kernel": f"{dom} ({'whole ring pass incl. merge/accumulate kernels' if world > 1 else 'call incl. its small helper kernels'})",
@@ -355,9 +363,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="default", choices=["default", "c5"],
                     help="c5 = the long-context ring config (not the driver's headline line)")
+    ap.add_argument("--causal", action="store_true", help="causal extension (not the driver's headline line)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     globals()["WORKLOAD"] = args.workload
+    globals()["CAUSAL"] = args.causal
     if args.impl == "reference":
         run_reference(args)
     else:
