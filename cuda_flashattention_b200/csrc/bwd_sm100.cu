@@ -487,10 +487,13 @@ template <int DR>
 static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 {
     using namespace bwd;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in shared-memory size is a per-device attribute of the function: set it once on every device used
+    static bool attr_set[64] = {};
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int Nq_pad = (a.Nq + 63) / 64 * 64, Hq = a.Hkv * a.G;
     CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;

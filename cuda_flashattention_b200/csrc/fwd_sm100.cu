@@ -414,10 +414,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 template <class C>
 static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in shared-memory size is a per-device attribute of the function: set it once on every device used
+    static bool attr_set[64] = {};
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(fwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const CUtensorMapDataType dt = C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     const CUtensorMapSwizzle v_swz = C::kF32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
