@@ -7,5 +7,5 @@ from ._lib import lib, LIB_PATH, EXPORTS, B200Error, B200_DTYPE_BF16, B200_DTYPE
 from .attention import (flash_attention_2_forward, flash_attention_2_backward, flash_attention,  # noqa: F401
                         lse_merge_, uses_tensor_cores, flash_attention_2_forward_host,
                         flash_attention_2_forward_backward_host, attention_forward, attention_backward,
-                        flash_attn_func)
+                        flash_attn_func, attention_varlen_forward, attention_varlen_backward, flash_attn_varlen_func)
 from .ring import RingComm, ring_attention_forward, ring_attention_backward, ring_kv_block, zigzag_rows  # noqa: F401

@@ -55,6 +55,8 @@ _SIGS = {
     "b200_fa2_bwd_ex": (_i, [_vp] * 9 + [_i, _i, _i, _i, _i, _f, _i, _i, _vp, _sz, _vp]),
     "b200_fa2_fwd_desc": (_i, [_dp, _vp, _vp, _vp, _vp, _fp, _vp]),
     "b200_fa2_bwd_desc": (_i, [_dp] + [_vp] * 9 + [_vp, _sz, _vp]),
+    "b200_fa2_fwd_varlen": (_i, [_dp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _fp, _vp]),
+    "b200_fa2_bwd_varlen": (_i, [_dp, _i, _vp, _vp] + [_vp] * 9 + [_vp]),
     "b200_fa2_fwd_host": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),

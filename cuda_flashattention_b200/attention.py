@@ -237,3 +237,81 @@ def flash_attn_func(q, k, v, causal=False, softmax_scale=None, layout="bnhd"):
     token-major order models use) or [B,H,N,d] (layout='bhnd'); any batch/head/row strides with a contiguous last
     dimension (e.g. slices of a packed qkv projection); Hkv may divide H (GQA / MQA)."""
     return _FlashAttnFn.apply(q, k, v, causal, softmax_scale, layout)
+
+
+# ---- packed variable-length batches (b200_fa2_fwd_varlen / b200_fa2_bwd_varlen) ----------------------
+def _cu_array(cu):
+    import ctypes as C
+    vals = [int(x) for x in (cu.tolist() if hasattr(cu, "tolist") else cu)]
+    if len(vals) < 1 or vals[0] != 0 or any(b < a for a, b in zip(vals, vals[1:])):
+        raise ValueError("cu_seqlens must start at 0 and be non-decreasing")
+    return (C.c_int * len(vals))(*vals), vals
+
+
+def _packed_desc(q, k, v, causal, softmax_scale):
+    for t in (q, k, v):
+        if t.dim() != 3 or t.stride(-1) != 1 or not t.is_cuda:
+            raise ValueError("expected packed CUDA tensors [total, heads, d] with a contiguous last dimension")
+    H, d = q.shape[1], q.shape[2]
+    Hkv = k.shape[1]
+    if k.shape[2] != d or tuple(v.shape) != tuple(k.shape) or H % Hkv != 0:
+        raise ValueError("q/k/v shape mismatch")
+    lay = lambda t: Layout(0, t.stride(1), t.stride(0))
+    return AttnDesc(B=1, H=H, Hkv=Hkv, Nq=0, Nkv=0, d=d, dtype=_dtype_code(q), flags=FLAG_CAUSAL if causal else 0,
+                    scale=float(softmax_scale or 0.0), q=lay(q), k=lay(k), v=lay(v)), lay
+
+
+def attention_varlen_forward(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, softmax_scale=None):
+    """q [total_q, H, d], k/v [total_k, Hkv, d]; sequence i = rows cu_seqlens[i] .. cu_seqlens[i+1]-1.
+    -> O [total_q, H, d], L [H, total_q]."""
+    desc, lay = _packed_desc(q, k, v, causal, softmax_scale)
+    cq, vq = _cu_array(cu_seqlens_q)
+    ck, vk = _cu_array(cu_seqlens_k)
+    if len(vq) != len(vk) or vq[-1] != q.shape[0] or vk[-1] != k.shape[0]:
+        raise ValueError("cu_seqlens do not match the packed tensors")
+    O = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+    L = torch.empty(q.shape[1], q.shape[0], dtype=torch.float32, device=q.device)
+    desc.o = lay(O)
+    with torch.cuda.device(q.device):
+        check(lib.b200_fa2_fwd_varlen(desc, len(vq) - 1, cq, ck, q.data_ptr(), k.data_ptr(), v.data_ptr(), O.data_ptr(),
+                                      L.data_ptr(), _stream()), "b200_fa2_fwd_varlen")
+    return O, L
+
+
+def attention_varlen_backward(q, k, v, O, L, dO, cu_seqlens_q, cu_seqlens_k, causal=False, softmax_scale=None):
+    desc, lay = _packed_desc(q, k, v, causal, softmax_scale)
+    cq, vq = _cu_array(cu_seqlens_q)
+    ck, vk = _cu_array(cu_seqlens_k)
+    if dO.stride(-1) != 1:
+        dO = dO.contiguous()
+    dQ = torch.empty(q.shape, dtype=q.dtype, device=q.device)
+    dK = torch.empty(k.shape, dtype=k.dtype, device=k.device)
+    dV = torch.empty(v.shape, dtype=v.dtype, device=v.device)
+    desc.o, desc.d_o, desc.dq, desc.dk, desc.dv = lay(O), lay(dO), lay(dQ), lay(dK), lay(dV)
+    with torch.cuda.device(q.device):
+        check(lib.b200_fa2_bwd_varlen(desc, len(vq) - 1, cq, ck, q.data_ptr(), k.data_ptr(), v.data_ptr(), O.data_ptr(),
+                                      L.data_ptr(), dO.data_ptr(), dQ.data_ptr(), dK.data_ptr(), dV.data_ptr(), _stream()),
+              "b200_fa2_bwd_varlen")
+    return dQ, dK, dV
+
+
+class _FlashAttnVarlenFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, cu_q, cu_k, causal, softmax_scale):
+        O, L = attention_varlen_forward(q, k, v, cu_q, cu_k, causal, softmax_scale)
+        ctx.save_for_backward(q, k, v, O, L)
+        ctx.cfg = (list(cu_q.tolist() if hasattr(cu_q, "tolist") else cu_q), list(cu_k.tolist() if hasattr(cu_k, "tolist") else cu_k),
+                   causal, softmax_scale)
+        return O
+
+    @staticmethod
+    def backward(ctx, dO):
+        q, k, v, O, L = ctx.saved_tensors
+        cu_q, cu_k, causal, softmax_scale = ctx.cfg
+        dQ, dK, dV = attention_varlen_backward(q, k, v, O, L, dO, cu_q, cu_k, causal, softmax_scale)
+        return dQ, dK, dV, None, None, None, None
+
+
+def flash_attn_varlen_func(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, softmax_scale=None):
+    """Differentiable attention over a packed batch of variable-length sequences (cu_seqlens on the host or any tensor)."""
+    return _FlashAttnVarlenFn.apply(q, k, v, cu_seqlens_q, cu_seqlens_k, causal, softmax_scale)

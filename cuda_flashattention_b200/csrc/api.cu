@@ -347,6 +347,90 @@ int b200_fa2_bwd_desc(const b200_attn_desc* p, const void* Q, const void* K, con
     return tc_bwd_strided(a, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
 }
 
+// ---- packed variable-length batches ------------------------------------------------------------------
+static int varlen_check(const b200_attn_desc* p, int n, const int* cq, const int* ck, int* max_q, int* max_k)
+{
+    if (!p || n < 0 || (n > 0 && (!cq || !ck)) || !valid_dtype(p->dtype) || p->H < 1 || p->Hkv < 1 || p->H % p->Hkv != 0 || p->d <= 0)
+        return B200_ERR_INVALID_ARGUMENT;
+    if ((p->flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    *max_q = *max_k = 0;
+    for (int i = 0; i < n; ++i) {
+        const int nq = cq[i + 1] - cq[i], nk = ck[i + 1] - ck[i];
+        if (nq < 0 || nk < 0 || ((nq == 0) != (nk == 0))) return B200_ERR_INVALID_ARGUMENT;
+        if ((p->flags & B200_FLAG_CAUSAL) && nq != nk) return B200_ERR_UNSUPPORTED;   // tensor-core causal path is square
+        if (nq > *max_q) *max_q = nq;
+        if (nk > *max_k) *max_k = nk;
+    }
+    return B200_OK;
+}
+// head / row strides of a packed [total, heads, d] tensor (all-zero layout = exactly that, contiguous)
+static Lay packed_lay(const b200_layout& l, int heads, int d)
+{
+    return lay_is_zero(l) ? Lay{0, (long long)d, (long long)heads * d} : Lay{0, l.head_stride, l.row_stride};
+}
+
+int b200_fa2_fwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, const int* cu_k, const void* Q, const void* K,
+                        const void* V, void* O, float* L, cudaStream_t st)
+{
+    int mq, mk;
+    B200_TRY(varlen_check(p, n_seqs, cu_q, cu_k, &mq, &mk));
+    if (n_seqs == 0 || mq == 0) return B200_OK;
+    if (!Q || !K || !V || !O || !L) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    const size_t es = p->dtype == B200_DTYPE_F32 ? 4 : 2;
+    const Lay lq = packed_lay(p->q, p->H, p->d), lk = packed_lay(p->k, p->Hkv, p->d), lv = packed_lay(p->v, p->Hkv, p->d),
+              lo = packed_lay(p->o, p->H, p->d);
+    const long long total_q = cu_q[n_seqs];
+    for (int i = 0; i < n_seqs; ++i) {
+        const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
+        if (nq == 0) continue;
+        FwdArgs a{(const uint8_t*)Q + (size_t)cu_q[i] * lq.sn * es, (const uint8_t*)K + (size_t)cu_k[i] * lk.sn * es,
+                  (const uint8_t*)V + (size_t)cu_k[i] * lv.sn * es, (uint8_t*)O + (size_t)cu_q[i] * lo.sn * es, L + cu_q[i],
+                  lq, lk, lv, lo, total_q, 1, p->H, p->Hkv, nq, nk, p->d, resolve_scale(p->scale, p->d), p->dtype,
+                  (p->flags & B200_FLAG_CAUSAL) != 0};
+        B200_TRY(tc_fwd_strided(a, st));
+    }
+    return B200_OK;
+}
+
+int b200_fa2_bwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, const int* cu_k, const void* Q, const void* K,
+                        const void* V, const void* O, const float* L, const void* dO, void* dQ, void* dK, void* dV,
+                        cudaStream_t st)
+{
+    int mq, mk;
+    B200_TRY(varlen_check(p, n_seqs, cu_q, cu_k, &mq, &mk));
+    if (n_seqs == 0 || mq == 0) return B200_OK;
+    if (!Q || !K || !V || !O || !L || !dO || !dQ || !dK || !dV) return B200_ERR_INVALID_ARGUMENT;
+    B200_TRY(device_check());
+    if (!tc_bwd_supported(p->dtype, p->d, mq, mk)) return B200_ERR_UNSUPPORTED;
+    const int H = p->H, d = p->d;
+    const size_t es = 2;
+    const Lay lq = packed_lay(p->q, H, d), lk = packed_lay(p->k, p->Hkv, d), lv = packed_lay(p->v, p->Hkv, d),
+              lo = packed_lay(p->o, H, d), ldo = packed_lay(p->d_o, H, d), ldq = packed_lay(p->dq, H, d),
+              ldk = packed_lay(p->dk, p->Hkv, d), ldv = packed_lay(p->dv, p->Hkv, d);
+    // one workspace, sized for the longest sequence; the sequences run back to back on the stream
+    void* ws;
+    const size_t need = bwd_ws_bytes(H, mq, mk, d, p->dtype);
+    B200_TRY(arena_get(need, &ws));
+    const long long total_q = cu_q[n_seqs];
+    for (int i = 0; i < n_seqs; ++i) {
+        const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
+        if (nq == 0) continue;
+        const size_t q0 = (size_t)cu_q[i], k0 = (size_t)cu_k[i];
+        float* D = reinterpret_cast<float*>(ws);
+        const size_t dbytes = (((size_t)H * nq * sizeof(float)) + 255) & ~(size_t)255;
+        const void* dOi = (const uint8_t*)dO + q0 * ldo.sn * es;
+        const void* Oi = (const uint8_t*)O + q0 * lo.sn * es;
+        B200_TRY(rowdot_strided(dOi, Oi, ldo, lo, D, 1, H, nq, d, p->dtype, st));
+        BwdArgs a{(const uint8_t*)Q + q0 * lq.sn * es, (const uint8_t*)K + k0 * lk.sn * es, (const uint8_t*)V + k0 * lv.sn * es, dOi,
+                  L + q0, D, (uint8_t*)dQ + q0 * ldq.sn * es, (uint8_t*)dK + k0 * ldk.sn * es, (uint8_t*)dV + k0 * ldv.sn * es,
+                  lq, lk, lv, ldo, ldq, ldk, ldv, 1, H, p->Hkv, nq, nk, d, resolve_scale(p->scale, d), p->dtype,
+                  (p->flags & B200_FLAG_CAUSAL) != 0, total_q};
+        B200_TRY(tc_bwd_strided(a, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st));
+    }
+    return B200_OK;
+}
+
 size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
 {
     if (B <= 0 || H <= 0 || Nq <= 0 || Nkv <= 0 || d <= 0 || !valid_dtype(dtype)) return 0;

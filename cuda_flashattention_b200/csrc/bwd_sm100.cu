@@ -407,13 +407,14 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 // (+inf, 0): a padded query row then has P = exp2(0 - inf) = 0 and dS = 0, so ragged Nq needs no masks.
 __global__ void __launch_bounds__(256)
 pad_stats_kernel(const float* __restrict__ L, const float* __restrict__ D, float* __restrict__ L2p, float* __restrict__ Dp,
-                 int Nq, int Nq_pad, size_t total)
+                 int Nq, int Nq_pad, size_t total, long long ldL)
 {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t bh = idx / Nq_pad;
     const int q = (int)(idx - bh * Nq_pad);
-    if (q < Nq) { L2p[idx] = L[bh * Nq + q] * 1.4426950408889634f; Dp[idx] = D[bh * Nq + q]; }
+    // ldL: floats between the L rows of consecutive (b,h) (Nq for the contiguous [B,H,Nq]; total_q for packed batches)
+    if (q < Nq) { L2p[idx] = L[bh * ldL + q] * 1.4426950408889634f; Dp[idx] = D[bh * Nq + q]; }
     else { L2p[idx] = INFINITY; Dp[idx] = 0.0f; }
 }
 
@@ -527,7 +528,7 @@ static BwdLaunch contiguous_launch(const void* Q, const void* K, const void* V, 
 
 // padded statistics + zeroed fp32 dQ accumulator in the workspace, one launch, then the cast (strided when dQ is)
 static int bwd_run(const BwdLaunch& a, int BHq, int d, void* ws, void* dQ, const Lay* ldq, int B, int H,
-                   const float* L, const float* Dvec, cudaStream_t st)
+                   const float* L, const float* Dvec, cudaStream_t st, long long ldL = 0)
 {
     using namespace bwd;
     const int Nq = a.Nq, Nq_pad = (Nq + 63) / 64 * 64;
@@ -537,7 +538,7 @@ static int bwd_run(const BwdLaunch& a, int BHq, int d, void* ws, void* dQ, const
     float* dQacc = reinterpret_cast<float*>(p);
     const size_t n_dq = (size_t)BHq * Nq * d;
     const size_t total = (size_t)BHq * Nq_pad;
-    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total, ldL > 0 ? ldL : Nq);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
@@ -582,7 +583,7 @@ int tc_bwd_strided(const BwdArgs& g, void* ws, size_t ws_bytes, cudaStream_t st)
     if (ws_bytes < tc_bwd_workspace_bytes(g.B * g.H, g.Nq, g.Nkv, g.d, g.dtype)) return B200_ERR_WORKSPACE;
     const BwdLaunch a{g.Q, g.K, g.V, g.dO, nullptr, nullptr, nullptr, g.dK, g.dV, g.lq, g.lk, g.lv, g.ldo, g.ldk, g.ldv,
                       g.B, g.Hkv, g.H / g.Hkv, g.B * g.Hkv, g.Nq, g.Nkv, g.scale, g.causal};
-    return bwd_run(a, g.B * g.H, g.d, ws, g.dQ, &g.ldq, g.B, g.H, g.L, g.D, st);
+    return bwd_run(a, g.B * g.H, g.d, ws, g.dQ, &g.ldq, g.B, g.H, g.L, g.D, st, g.ldL);
 }
 
 // ---- pieces for the ring backward: statistics once per call; per ring step one launch that adds
@@ -603,7 +604,7 @@ int tc_bwd_ring_prepare(const float* L, const float* Dvec, void* stats, int BH, 
     float* L2p = reinterpret_cast<float*>(stats);
     float* Dp = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(stats) + al256((size_t)BH * Nq_pad * sizeof(float)));
     const size_t total = (size_t)BH * Nq_pad;
-    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total);
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, Dvec, L2p, Dp, Nq, Nq_pad, total, Nq);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;

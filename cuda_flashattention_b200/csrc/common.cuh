@@ -42,10 +42,11 @@ struct FwdArgs {
     int B, H, Hkv, Nq, Nkv, d; float scale; int dtype; bool causal;
 };
 struct BwdArgs {
-    const void *Q, *K, *V, *dO; const float *L, *D;   // L, D contiguous [B*H, Nq]
+    const void *Q, *K, *V, *dO; const float *L, *D;   // D contiguous [B*H, Nq]; L rows ldL apart
     void *dQ, *dK, *dV;
     Lay lq, lk, lv, ldo, ldq, ldk, ldv;
     int B, H, Hkv, Nq, Nkv, d; float scale; int dtype; bool causal;
+    long long ldL = 0;                                 // floats between consecutive (b,h) rows of L; 0 = Nq
 };
 
 // ---- generic CUDA-core kernels (generic_simt.cu) ------------------------------------------------

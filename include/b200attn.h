@@ -138,6 +138,18 @@ B200_API int b200_fa2_bwd_desc(const b200_attn_desc* desc, const void* Q, const 
                       const float* L, const void* dO, void* dQ, void* dK, void* dV, void* workspace, size_t workspace_bytes,
                       cudaStream_t stream);
 
+/* ---- packed variable-length batches ------------------------------------------------
+ * Q/O/dO/dQ are [total_q, H, d], K/V/dK/dV [total_k, Hkv, d] (head / row strides from the descriptor's layouts, all
+ * zero = contiguous; batch strides, B, Nq, Nkv are ignored); sequence i is rows cu_seqlens[i] .. cu_seqlens[i+1]-1
+ * (HOST arrays of n_seqs + 1 ints).  L is [H, total_q] fp32.  One launch sequence per batch entry on the tensor-core
+ * kernels (d in {64,128}; backward bf16; causal needs equal q / k lengths); the backward takes its scratch from the
+ * library's arena. */
+B200_API int b200_fa2_fwd_varlen(const b200_attn_desc* desc, int n_seqs, const int* cu_seqlens_q, const int* cu_seqlens_k,
+                        const void* Q, const void* K, const void* V, void* O, float* L, cudaStream_t stream);
+B200_API int b200_fa2_bwd_varlen(const b200_attn_desc* desc, int n_seqs, const int* cu_seqlens_q, const int* cu_seqlens_k,
+                        const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                        void* dQ, void* dK, void* dV, cudaStream_t stream);
+
 /* ---- host-buffer entry points --------------------------------------------------------------------
  * The reference's drivers own HOST arrays and copy them to the device around every call
  * (src/02_flash_attention_v2_forward/main.cu:42-64, src/02_flash_attention_v2_backward/main.cu:261-289).

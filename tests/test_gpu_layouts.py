@@ -120,3 +120,33 @@ def test_autograd_function_matches_a_float32_torch_reference():
     for got, want in ((qa.grad, qr.grad), (ka.grad, kr.grad), (va.grad, vr.grad)):
         assert rel_l2(host(got), host(want)) <= 1e-2
         assert (got.float() - want).abs().max().item() <= 2e-2 * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("causal,Hkv", [(False, 2), (True, 4), (False, 1)])
+def test_packed_variable_length_batch(causal, Hkv):
+    # three sequences of different lengths in one packed [total, H, d] batch (cross lengths when not causal)
+    H, d = 4, 128
+    lens_q = [200, 64, 333]
+    lens_k = lens_q if causal else [260, 64, 130]
+    cu_q, cu_k = np.concatenate([[0], np.cumsum(lens_q)]), np.concatenate([[0], np.cumsum(lens_k)])
+    q, do = _rand((cu_q[-1], H, d), 1), _rand((cu_q[-1], H, d), 2)
+    k, v = _rand((cu_k[-1], Hkv, d), 3), _rand((cu_k[-1], Hkv, d), 4)
+    O, L = fa.attention_varlen_forward(q, k, v, cu_q, cu_k, causal=causal)
+    dQ, dK, dV = fa.attention_varlen_backward(q, k, v, O, L, do, cu_q, cu_k, causal=causal)
+    G = H // Hkv
+    for i in range(len(lens_q)):
+        sq, sk = slice(cu_q[i], cu_q[i + 1]), slice(cu_k[i], cu_k[i + 1])
+        for hk in range(Hkv):
+            dK_ref = dV_ref = None
+            for g in range(G):
+                h = hk * G + g
+                args = (host(q[sq, h]), host(k[sk, hk]), host(v[sk, hk]))
+                Oo, Lo = oracle.forward(*args, 0.0, causal=causal)
+                scl = max(1.0, float(np.abs(Oo).max()))
+                assert np.abs(host(O[sq, h]) - Oo).max() <= 2e-2 * scl and np.abs(host(L[h, sq]) - Lo).max() <= 2e-2
+                rq, rk, rv = oracle.backward(*args, host(do[sq, h]), 0.0, causal=causal)
+                assert rel_l2(host(dQ[sq, h]), rq) <= 1e-2
+                dK_ref = rk if dK_ref is None else dK_ref + rk
+                dV_ref = rv if dV_ref is None else dV_ref + rv
+            assert rel_l2(host(dK[sk, hk]), dK_ref) <= 1e-2 and rel_l2(host(dV[sk, hk]), dV_ref) <= 1e-2
+            assert np.abs(host(dV[sk, hk]) - dV_ref).max() <= 2e-2 * max(1.0, float(np.abs(dV_ref).max()))
