@@ -11,3 +11,12 @@ rm -rf /tmp/b200_mpi; echo "=== 04_ring ($N ranks)"
 for r in $(seq 0 $((N-1))); do RANK=$r WORLD_SIZE=$N timeout 300 ./04_ring > 04_ring.$r.log 2>&1 & done
 wait
 grep -E "PASS|FAIL|match|Total significant" 04_ring.0.log | tail -5
+# the reference's communication diagnostics (ring pass-around, compute/transfer overlap) need >= 2 ranks
+if [ "$N" -ge 2 ]; then
+  for p in 01_nccl_verify 02_overlap; do
+    rm -rf /tmp/b200_mpi; echo "=== $p ($N ranks)"
+    for r in $(seq 0 $((N-1))); do RANK=$r WORLD_SIZE=$N timeout 120 ./$p > $p.$r.log 2>&1 & done
+    wait
+    grep -E "Received|completed|Total time" $p.0.log | tail -6
+  done
+fi
