@@ -149,7 +149,9 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t slab = (size_t)N * d * es, lslab = (size_t)N * sizeof(float);
     // chunk = as many (b,h) slabs as give ~32 MB per tensor: small enough to pipeline, large enough to fill the GPU
-    int hc = (int)(((size_t)32 << 20) / slab);
+    static size_t chunk_bytes = 0;                 // tuning hook: B200_HOST_CHUNK_MB
+    if (!chunk_bytes) { const char* e = getenv("B200_HOST_CHUNK_MB"); chunk_bytes = (size_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20; }
+    int hc = (int)(chunk_bytes / slab);
     if (hc < 1) hc = 1;
     if (hc > BH) hc = BH;
     const int nchunks = (BH + hc - 1) / hc;
