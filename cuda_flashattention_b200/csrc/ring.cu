@@ -424,7 +424,7 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     // in 4 GB (it does for every shape in BASELINE.json): no step then waits for a merge -- they are all folded by one
     // n-way merge at the end -- and each attention kernel can start in the tail of the previous one.
     const size_t part_bytes = align256(kv_bytes) + align256(l_bytes);
-    int NB = (int)std::min<size_t>((size_t)nranks, std::max<size_t>(2, ((size_t)4 << 30) / part_bytes));
+    int NB = (int)std::min<size_t>((size_t)std::min(nranks, 32), std::max<size_t>(2, ((size_t)4 << 30) / part_bytes));   // (merge: <= 32 partials)
     if (const char* e = getenv("B200_RING_MAX_PARTIALS")) NB = std::max(2, std::min(NB, atoi(e)));   // test hook (same on all ranks)
     const size_t total = 4 * align256(kv_bytes) + (size_t)NB * part_bytes;
     void* base;
