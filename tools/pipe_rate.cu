@@ -12,6 +12,10 @@ __device__ __forceinline__ float ffma(float a, float b, float c) { float d; asm 
 __device__ __forceinline__ float fmx(float a, float b) { float d; asm volatile("max.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b)); return d; }
 __device__ __forceinline__ float fmx3(float a, float b, float c) { float d; asm volatile("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; }
 __device__ __forceinline__ uint32_t pk(float a, float b) { uint32_t r; asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ uint32_t ex2h2(uint32_t x) { uint32_t y; asm volatile("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(x)); return y; }
+__device__ __forceinline__ uint32_t ex2b2(uint32_t x) { uint32_t y; asm volatile("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x)); return y; }
+__device__ __forceinline__ uint32_t pkh(float a, float b) { uint32_t r; asm volatile("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ uint32_t hfma2(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 __device__ __forceinline__ uint32_t lea(uint32_t a, uint32_t b) { uint32_t r; asm volatile("{ .reg .u32 t; shl.b32 t, %1, 23; add.u32 %0, t, %2; }" : "=r"(r) : "r"(a), "r"(b)); return r; }
 
 // OP: which instruction; CH: number of independent chains (ILP)
@@ -43,6 +47,10 @@ __global__ void k(float* out, long long* cyc, float seed)
                 if (OP == 9) { v[i] = ex2(v[i]); w[i] = f2_fma(w[i], C1, C2); w[i] = f2_add(w[i], C2); u[i] = pk(__uint_as_float(u[i]), c1); }
                 if (OP == 10) { w[i] = f2_fma(w[i], C1, C2); u[i] = lea(u[i], u[i]); }               // FMA pipe + ALU pipe
                 if (OP == 11) { v[i] = ffma(v[i], c1, c2); u[i] = lea(u[i], u[i]); }
+                if (OP == 12) u[i] = ex2h2(u[i]);                                                    // 2 x MUFU.EX2.F16 (one per half)
+                if (OP == 13) u[i] = ex2b2(u[i]);                                                    // 2 x MUFU.EX2.BF16
+                if (OP == 14) u[i] = pkh(__uint_as_float(u[i]), c1);                                 // F2FP.F16.F32.PACK_AB
+                if (OP == 15) u[i] = hfma2(u[i], u[i], u[i]);                                        // HFMA2
             }
     }
     const long long t1 = clock64();
@@ -67,6 +75,7 @@ int main()
     float* out; long long* cyc;
     cudaMalloc(&out, 4096 * 4); cudaMalloc(&cyc, 8);
     RUN(0, "FFMA") RUN(1, "FFMA2") RUN(2, "FADD2") RUN(3, "MUFU.EX2") RUN(4, "FMNMX") RUN(5, "FMNMX3") RUN(6, "F2FP.BF16.PACK") RUN(7, "SHL+IADD (LEA)")
+    RUN(12, "ex2.f16x2 (2 MUFU.EX2.F16)") RUN(13, "ex2.bf16x2 (2 MUFU.EX2.BF16)") RUN(14, "F2FP.F16.PACK") RUN(15, "HFMA2")
     RUN(8, "MUFU + FFMA2") RUN(9, "MUFU+FFMA2+FADD2+F2FP") RUN(10, "FFMA2 + LEA") RUN(11, "FFMA + LEA")
     return 0;
 }
