@@ -185,7 +185,10 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         float* dst = dQacc + (bh * dq_rows + (size_t)qt * BM) * DR + r;   // (dq_rows: rows per slab of the accumulator)
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
         if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
-            if (q_valid == BM) {
+            if (dbg & 2) {                                             // experiment: plain stores, same bytes, no L2 atomic
+#pragma unroll
+                for (int q = 0; q < BM; ++q) dst[q * DR] = __uint_as_float(v[q]);
+            } else if (q_valid == BM) {
 #pragma unroll
                 for (int q = 0; q < BM; ++q) red_add_f32(dst + q * DR, __uint_as_float(v[q]));
             } else {
@@ -507,8 +510,9 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
         make_tmap_4d(&tmdV, a.dV, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldv.sb, a.ldv.sh, a.ldv.sn, BN, 64))
         return B200_ERR_CUDA;
     dim3 grid((a.Nkv + BN - 1) / BN, a.Hkv, a.Bm);
-    static int dbg = -1;                 // experiment hook (B200_BWD_DBG bit 0: skip the dQ reduce-add -> wrong dQ, timing only)
-    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 1) : 0; }
+    // experiment hook, timing only (wrong dQ): B200_BWD_DBG bit 0 skips the dQ reduce-adds, bit 1 issues plain stores instead
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 3) : 0; }
     bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
                                                 a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
                                                 a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
