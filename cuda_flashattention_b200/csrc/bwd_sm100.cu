@@ -40,7 +40,18 @@ constexpr int THREADS = 512;
 // smem carve-up (offsets from the 1024-aligned base)
 constexpr int OFF_K = 0, OFF_V = OFF_K + KV_TILE, OFF_Q = OFF_V + KV_TILE, OFF_DO = OFF_Q + NS * Q_TILE;
 constexpr int OFF_DS = OFF_DO + NS * Q_TILE, OFF_STAT = OFF_DS + 2 * DS_TILE;
+#ifndef B200_DQ_RED
+// dQ leaves through staging buffers and bulk reduce-adds (cp.reduce.async.bulk): STG_NBUF buffers of STG_ROWS q rows,
+// used round-robin.  (-DB200_DQ_RED builds the r1(b) drain instead: per-warp red.global.add from registers.)
+#ifndef B200_STG_ROWS
+#define B200_STG_ROWS 32
+#endif
+constexpr int STG_ROWS = B200_STG_ROWS, STG_NBUF = BM / STG_ROWS, STG_BYTES = STG_ROWS * D * 4;
+constexpr int OFF_STG = OFF_STAT + NS * 2 * STAT_BYTES;
+constexpr int OFF_BAR = OFF_STG + STG_NBUF * STG_BYTES;
+#else
 constexpr int OFF_BAR = OFF_STAT + NS * 2 * STAT_BYTES;
+#endif
 constexpr int NBARS = 1 + 2 * NS + 2 + 1 + 2 + 1 + 2 + 1;
 constexpr int SMEM = 1024 + OFF_BAR + NBARS * 8 + 16;
 static_assert(SMEM <= 227 * 1024, "backward shared memory budget");
@@ -60,6 +71,10 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
 
 __device__ __forceinline__ void lds_f32x4(float* dst, uint32_t saddr) {
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(dst[0]), "=f"(dst[1]), "=f"(dst[2]), "=f"(dst[3]) : "r"(saddr));
+}
+__device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, const void* ssrc, uint32_t bytes) {
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                 ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
     asm volatile("red.relaxed.gpu.global.add.f32 [%0], %1;" ::"l"(gaddr), "f"(v) : "memory");
@@ -159,7 +174,7 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
 template <int DR>
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
                                                float* __restrict__ dQacc, int Nq, int dq_rows, int n_tot, int n_it, int qt_min,
-                                               int i_off, size_t bhq0, int dbg)
+                                               int i_off, size_t bhq0, int dbg, uint8_t* smem)
 {
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
@@ -184,6 +199,28 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         B200_TRB(1, i, 1);
         float* dst = dQacc + (bh * dq_rows + (size_t)qt * BM) * DR + r;   // (dq_rows: rows per slab of the accumulator)
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
+#ifndef B200_DQ_RED
+        if (!(dbg & 1)) {
+            const bool leader = (threadIdx.x & 127) == 0;
+#pragma unroll
+            for (int half = 0; half < BM / STG_ROWS; ++half) {
+                float* stg = reinterpret_cast<float*>(smem + OFF_STG + half * STG_BYTES);
+                if (leader) tma_store_wait_read<STG_NBUF - 1>();       // the reduce that last used this buffer has read it
+                named_bar_sync(6, 128);
+                if (r < DR) {
+#pragma unroll
+                    for (int q = 0; q < STG_ROWS; ++q) stg[q * DR + r] = __uint_as_float(v[STG_ROWS * half + q]);
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(6, 128);
+                if (leader) {
+                    const int rows = min(STG_ROWS, q_valid - STG_ROWS * half);
+                    if (rows > 0) bulk_reduce_add_f32(dst - r + (size_t)STG_ROWS * half * DR, stg, (uint32_t)rows * DR * 4);
+                    tma_store_commit();
+                }
+            }
+        }
+#else
         if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
             if (dbg & 2) {                                             // experiment: plain stores, same bytes, no L2 atomic
 #pragma unroll
@@ -196,8 +233,12 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
                 for (int q = 0; q < BM; ++q) if (q < q_valid) red_add_f32(dst + q * DR, __uint_as_float(v[q]));
             }
         }
+#endif
         B200_TRB(1, i, 2);
     }
+#ifndef B200_DQ_RED
+    if ((threadIdx.x & 127) == 0) tma_store_wait<0>();
+#endif
 }
 
 // dV (w = 0) / dK (w = 1) epilogue: TMEM fp32 [128 kv x 128 d] -> bf16 -> swizzled smem -> TMA store.
@@ -397,7 +438,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         tc_fence_after();
         bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, hk, b);
     } else if (warp >= 12) {
-        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, dq_rows, n_tot, n_it, qt_min, i_off, bhq0, dbg);
+        bwd_drain_role<DR>(tmem, bar_dQ_full, bar_dQ_empty, dQacc, Nq, dq_rows, n_tot, n_it, qt_min, i_off, bhq0, dbg, smem);
     }
 
     tc_fence_before();
