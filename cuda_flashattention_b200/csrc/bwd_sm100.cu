@@ -1,5 +1,5 @@
-// bwd_sm100.cu -- FlashAttention-2 backward for sm_100a (bf16, d = 128): dK/dV-stationary CTAs,
-// tcgen05 MMAs with every accumulator in TMEM, dQ reduced into an fp32 buffer by coalesced red.global.add.
+// bwd_sm100.cu -- FlashAttention-2 backward for sm_100a (bf16, d = 128 or 64): dK/dV-stationary CTAs,
+// tcgen05 MMAs with every accumulator in TMEM, dQ reduced into an fp32 buffer by bulk add-reductions.
 //
 // Replaces flash_attention_2_backward_kernel (reference
 // src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:47-246).  Same math --
@@ -17,7 +17,10 @@
 //   M3  dV  += P^T dO_i             TS   A = P^T from TMEM, B = dO_i as an MN-major operand
 //   M4  dK  += dS^T Q_i             TS   A = dS^T from TMEM, B = Q_i as an MN-major operand
 //   M5  dQ_i^T = K^T dS             SS   A = K (MN-major view), B = dS^T smem (MN-major) -> TMEM dQ
-//   drain warpgroup: dQ_i^T TMEM -> registers -> coalesced fp32 red.global.add into the dQ accumulator
+//   drain warpgroup: dQ_i^T TMEM -> registers -> two alternating 16 KB staging buffers ([q][d] fp32)
+//                    -> cp.reduce.async.bulk (add.f32) into the fp32 dQ accumulator
+// Extensions on the same kernel: causal mask (diagonal q tiles), grouped K/V heads (the CTA of a K/V head walks
+// the q tiles of all its query heads), strided layouts (4-D tensor maps), d = 64 (half-width tiles).
 // TMEM columns: S[0] 0..63, S[1] 64..127, dP 128..191, dQ^T 192..255, dV 256..383, dK 384..511.
 // Issue order per iteration i:  M1(i+1) | M3(i) M4(i) | M2(i+1) | M5(i)   (see DESIGN.md for the slack analysis)
 //
@@ -168,9 +171,11 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
     }
 }
 
-// dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> registers -> fp32 red.global.add straight
-// into the dQ accumulator.  A warp's 32 lanes hold 32 consecutive d of one q row, so every red
-// instruction is one coalesced 128-byte reduction; nothing goes through shared memory.
+// dQ drain warpgroup: TMEM dQ_i^T [128 d lanes x 64 q] -> registers -> staging buffer ([q][d] fp32: a warp's 32
+// lanes hold 32 consecutive d of one q row, so every st.shared is one conflict-free 128-byte row segment) -> one
+// cp.reduce.async.bulk add-reduction of 32 contiguous accumulator rows per buffer.  The TMEM columns are released
+// right after the load, so the next dQ MMA never waits for the reductions.  (-DB200_DQ_RED: per-warp red.global.add
+// from registers instead -- the LSU store path carrying that stream cost 17 % of the kernel)
 template <int DR>
 __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_full, uint64_t* bar_dQ_empty,
                                                float* __restrict__ dQacc, int Nq, int dq_rows, int n_tot, int n_it, int qt_min,
