@@ -83,3 +83,32 @@ def test_zigzag_causal_ring_schedule_covers_the_causal_triangle_evenly():
                     seen.add((q, k))
             want = {(q, k) for q in mine for k in range(2 * P) if k <= q}
             assert seen == want
+
+
+def test_descriptor_and_varlen_argument_checks_without_device():
+    # argument validation of the extended entry points happens before any device call
+    import ctypes as C
+    from cuda_flashattention_b200._lib import AttnDesc
+    d = AttnDesc(B=1, H=6, Hkv=4, Nq=64, Nkv=64, d=128, dtype=0, flags=0, scale=0.0)     # 6 % 4 != 0
+    assert fa.lib.b200_fa2_fwd_desc(d, 8, 8, 8, 8, 8, None) == -1
+    d.Hkv = 2
+    d.flags = 2                                                                          # unknown flag bit
+    assert fa.lib.b200_fa2_fwd_desc(d, 8, 8, 8, 8, 8, None) == -1
+    d.flags, d.Nq, d.Nkv = 1, 128, 64                                                    # causal needs Nq <= Nkv
+    assert fa.lib.b200_fa2_fwd_desc(d, 8, 8, 8, 8, 8, None) == -1
+    assert fa.lib.b200_fa2_bwd_desc(d, *([8] * 9), None, 0, None) == -1
+    d.B = 0                                                                              # empty batch: no-op
+    d.flags, d.Nq = 0, 64
+    assert fa.lib.b200_fa2_fwd_desc(d, None, None, None, None, None, None) == 0
+    # packed batches: lengths must be non-negative; causal needs equal q / k lengths
+    d = AttnDesc(B=1, H=4, Hkv=4, Nq=0, Nkv=0, d=128, dtype=0, flags=0, scale=0.0)
+    bad = (C.c_int * 3)(0, 10, 5)
+    ok = (C.c_int * 3)(0, 10, 30)
+    ok_k = (C.c_int * 3)(0, 10, 40)
+    assert fa.lib.b200_fa2_fwd_varlen(d, 2, bad, bad, 8, 8, 8, 8, 8, None) == -1
+    d.flags = 1
+    assert fa.lib.b200_fa2_fwd_varlen(d, 2, ok, ok_k, 8, 8, 8, 8, 8, None) == -8         # unsupported: causal with Nq != Nkv
+    assert fa.lib.b200_fa2_fwd_varlen(d, 0, None, None, None, None, None, None, None, None) == 0
+    # ring: unknown flags / bad ranks are rejected before anything else
+    assert fa.lib.b200_ring_fwd_ex(8, 8, 8, 8, 8, 1, 1, 64, 128, 0.0, 0, 4, None, 0, 2, None) == -1
+    assert fa.lib.b200_ring_zigzag_chunk(3, 0, 2) == -1
