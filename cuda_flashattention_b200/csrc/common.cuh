@@ -72,6 +72,7 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
            float scale, int dtype, cudaStream_t st, bool causal = false);
 // strided / grouped-head form (tensor-core shapes only: tc_fwd_supported, 16-byte aligned bases and strides)
 int tc_fwd_strided(const FwdArgs& a, cudaStream_t st);
+int launch_fwd_split(const FwdArgs& a, int BH_valid, cudaStream_t st);   // experimental variant (fwd_split_sm100.cu), bf16 d = 128
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
