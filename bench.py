@@ -166,7 +166,10 @@ def cpu_sample(n_heads, N, d):
     return time.perf_counter() - t0, ("reference" if use_ref else "port")
 
 
-def cpu_baseline(N=768, d=D0):
+CPU_SAMPLE_N = 1024          # rows per head of the bounded CPU sample (the reference's backward is O(N^3): ~2 s per head)
+
+
+def cpu_baseline(N=CPU_SAMPLE_N, d=D0):
     cores = os.cpu_count() or 1
     heads = min(cores, 32)
     secs, kind = cpu_sample(heads, N, d)
@@ -179,7 +182,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    N = 512                                    # the naive backward is O(N^3): keep each step a few seconds
+    N = CPU_SAMPLE_N                           # the naive backward is O(N^3): keep each step a few seconds
     for _ in range(args.warmup):
         cpu_sample(min(os.cpu_count() or 1, 32), 256, D0)
     times, kind, heads = [], "port", min(os.cpu_count() or 1, 32)

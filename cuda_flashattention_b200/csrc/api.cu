@@ -2,14 +2,15 @@
 // between the tcgen05 tensor-core kernels and the generic CUDA-core kernels, scratch arena.
 #include "common.cuh"
 #include <math.h>
+#include <atomic>
 #include <mutex>
 
 namespace b200 {
 
 static thread_local int g_last_cuda_error = 0;
 void set_last_cuda_error(int code) { g_last_cuda_error = code; }
-static unsigned long long g_launches = 0;
-void count_launch(int n) { g_launches += (unsigned long long)n; }
+static std::atomic<unsigned long long> g_launches{0};     // callers may launch from several host threads
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 struct Arena { void* ptr = nullptr; size_t bytes = 0; };
 static Arena g_arena[64];
@@ -224,7 +225,7 @@ const char* b200_strerror(int s)
 }
 int b200_last_cuda_error(void) { return g_last_cuda_error; }
 int b200_version(void) { return 100; }
-unsigned long long b200_debug_launch_count(void) { return g_launches; }
+unsigned long long b200_debug_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 #ifdef B200_TRACE
 }
 namespace b200 { int fwd_trace_read(long long* out, int n); int bwd_trace_read(long long* out, int n); }

@@ -21,6 +21,11 @@
  *     (The reference returns void and drops errors; see b200_strerror.)
  *   - There is no CPU fallback: without a CUDA device / on a non-sm_100 device the calls fail with
  *     B200_ERR_NO_DEVICE / B200_ERR_ARCH.
+ *   - Threads and streams: the calls may be made from several host threads.  The internal scratch
+ *     arena is ONE buffer per device, reused by every call that is given workspace = NULL, so such
+ *     calls must be ordered on the device (same stream, or event dependencies); calls that are meant
+ *     to overlap on different streams of one device pass their own workspace
+ *     (b200_fa2_bwd_workspace_bytes).  A call that has to grow the arena synchronises the device.
  */
 #ifndef B200ATTN_H_
 #define B200ATTN_H_
