@@ -462,6 +462,10 @@ static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
         if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
         if (a.d == 128) {
             if (variant == 2) return launch_fwd_split(a, BH_valid, st);       // experimental: split-S pipeline
+            if (variant == 3) {                                               // experimental: CTA pairs (cta_group::2)
+                if (fwd_pair_eligible(a)) return launch_fwd_pair(a, BH_valid, st);
+                return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true>>(a, BH_valid, st);
+            }
             switch (variant) {
 #define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(a, BH_valid, st);
                 B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)

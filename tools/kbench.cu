@@ -1,7 +1,9 @@
 // kbench.cu -- native micro-harness for the C-ABI (no Python/torch start-up): device-resident
 // N(0,1) inputs, CUDA-event timing of b200_fa2_fwd / b200_fa2_bwd, optional in-kernel trace dump
 // (library built with EXTRA=-DB200_TRACE).  Not the contract bench (that is bench.py).
-//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal]
+//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal] [--check]
+//   --check: before timing, compare the forward (O, L) of the selected kernel (e.g. B200_FWD_VARIANT) with the
+//            library's generic CUDA-core kernels on the same inputs (b200_debug_force_generic); exit 5 on mismatch
 //   env B200ATTN_LIB = path of the shared object (default: cuda_flashattention_b200/libb200attn.so)
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
@@ -40,6 +42,7 @@ typedef int (*bwdx_t)(const void*, const void*, const void*, const void*, const 
                       int, int, int, int, int, float, int, int, void*, size_t, cudaStream_t);
 typedef size_t (*ws_t)(int, int, int, int, int, int);
 typedef int (*trace_t)(long long*, int);
+typedef int (*force_t)(int);
 
 int main(int argc, char** argv)
 {
@@ -47,9 +50,10 @@ int main(int argc, char** argv)
     const char* mode = argv[1];
     const int B = atoi(argv[2]), H = atoi(argv[3]), N = atoi(argv[4]), d = atoi(argv[5]);
     const bool f32 = strcmp(argv[6], "f32") == 0;
-    int iters = 10; bool trace = false, causal = false;
+    int iters = 10; bool trace = false, causal = false, check = false;
     for (int i = 7; i < argc; ++i) {
-        if (!strcmp(argv[i], "--trace")) trace = true; else if (!strcmp(argv[i], "--causal")) causal = true; else iters = atoi(argv[i]);
+        if (!strcmp(argv[i], "--trace")) trace = true; else if (!strcmp(argv[i], "--causal")) causal = true;
+        else if (!strcmp(argv[i], "--check")) check = true; else iters = atoi(argv[i]);
     }
     const char* path = getenv("B200ATTN_LIB");
     if (!path) path = "cuda_flashattention_b200/libb200attn.so";
@@ -82,6 +86,39 @@ int main(int argc, char** argv)
     auto run_b = [&]() { int s = causal ? bwdx(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, 1, ws, wsn, 0)
                                           : bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, ws, wsn, 0); if (s) { fprintf(stderr, "bwd status %d\n", s); exit(3); } };
     run_f();
+    if (check) {
+        // forward parity of the selected tensor-core kernel against the generic CUDA-core kernels (fp32 math)
+        force_t force = (force_t)dlsym(h, "b200_debug_force_generic");
+        if (!force) { fprintf(stderr, "missing b200_debug_force_generic\n"); return 2; }
+        CK(cudaDeviceSynchronize());
+        std::vector<uint8_t> o1(n * eb), o2(n * eb);
+        std::vector<float> l1((size_t)B * H * N), l2((size_t)B * H * N);
+        CK(cudaMemcpy(o1.data(), O, n * eb, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(l1.data(), L, l1.size() * 4, cudaMemcpyDeviceToHost));
+        force(1); run_f(); force(0);
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(o2.data(), O, n * eb, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(l2.data(), L, l2.size() * 4, cudaMemcpyDeviceToHost));
+        auto val = [&](const std::vector<uint8_t>& v, size_t i) -> double {
+            if (f32) return ((const float*)v.data())[i];
+            uint32_t u = (uint32_t)((const uint16_t*)v.data())[i] << 16; float f; memcpy(&f, &u, 4); return f;
+        };
+        double max_o = 0, max_l = 0, num = 0, den = 0; size_t bad = 0;
+        for (size_t i = 0; i < n; ++i) {
+            const double a = val(o1, i), b = val(o2, i), e = fabs(a - b);
+            if (!(e <= 1e30)) ++bad;
+            if (e > max_o) max_o = e;
+            num += e * e; den += b * b;
+        }
+        for (size_t i = 0; i < l1.size(); ++i) { const double e = fabs((double)l1[i] - l2[i]); if (!(e <= 1e30)) ++bad; if (e > max_l) max_l = e; }
+        const double rel = sqrt(num / (den > 0 ? den : 1));
+        const double tol = f32 ? 2e-3 : 2e-2;
+        const bool ok = bad == 0 && max_o <= tol && max_l <= tol && rel <= 1e-2;
+        printf("check vs generic kernels: max|dO| %.3e  rel-L2 %.3e  max|dL| %.3e  non-finite %zu  -> %s\n", max_o, rel, max_l, bad,
+               ok ? "PASS" : "FAIL");
+        if (!ok) return 5;
+        run_f();
+    }
     for (int i = 0; i < 3; ++i) { if (do_f) run_f(); if (do_b) run_b(); }
     CK(cudaDeviceSynchronize());
     std::vector<float> tf, tb;
