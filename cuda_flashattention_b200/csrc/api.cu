@@ -228,9 +228,13 @@ int b200_version(void) { return 100; }
 unsigned long long b200_debug_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 #ifdef B200_TRACE
 }
-namespace b200 { int fwd_trace_read(long long* out, int n); int bwd_trace_read(long long* out, int n); }
+namespace b200 { int fwd_trace_read(long long* out, int n); int bwd_trace_read(long long* out, int n); int dbuf_trace_read(long long* out, int n); }
 extern "C" {
-__attribute__((visibility("default"))) int b200_debug_trace_read(long long* out, int n) { return b200::fwd_trace_read(out, n); }
+__attribute__((visibility("default"))) int b200_debug_trace_read(long long* out, int n)
+{
+    const char* e = getenv("B200_FWD_VARIANT");           // the experimental double-buffered forward keeps its own trace
+    return (e && atoi(e) == 4) ? b200::dbuf_trace_read(out, n) : b200::fwd_trace_read(out, n);
+}
 __attribute__((visibility("default"))) int b200_debug_trace_read_bwd(long long* out, int n) { return b200::bwd_trace_read(out, n); }
 #endif
 int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generic = on ? 1 : 0; return old; }

@@ -24,7 +24,7 @@
 //
 // STATUS: written at the end of round 1 after the GPU budget of the round was spent: it compiles for sm_100a and its
 // SASS has been inspected (UTCHMMA.2CTA / UTMALDG.2CTA / UTCBAR.2CTA.MULTICAST present), but it has NOT been run on
-// a B200 yet.  It is never selected by default; tools/try_fwd_pair.sh is the first thing to run on a GPU box
+// a B200 yet.  It is never selected by default; tools/try_fwd_variant.sh 3 is the first thing to run on a GPU box
 // (parity against the generic CUDA-core kernels, then timing against the default kernel).
 #include "common.cuh"
 #include "ptx.cuh"

@@ -32,7 +32,9 @@ __device__ long long g_trace[3 * 8 * 8];
 
 // POLY = how many of every 16 (score, score) pairs get their exp2 from the FMA-pipe polynomial
 // instead of the MUFU (bf16 only); SPLITP = P is published to the MMA warp in two halves.
-template <typename Elem_, int D_, int NT_, int BC_, int POLY_ = 0, bool SPLITP_ = true>
+// ISSUERS = 2 (experimental, NT = 2 only): one MMA-issuing thread per query tile (warps 1 and 3) instead of one thread
+// serving both tiles in turn.
+template <typename Elem_, int D_, int NT_, int BC_, int POLY_ = 0, bool SPLITP_ = true, int ISSUERS_ = 1>
 struct FwdCfg {
     using Elem = Elem_;
     static constexpr int EB = sizeof(Elem);
@@ -46,6 +48,8 @@ struct FwdCfg {
     static constexpr int THREADS = 128 + NT * 128;
     static constexpr int POLY = POLY_;
     static constexpr bool SPLITP = SPLITP_;
+    static constexpr int ISSUERS = ISSUERS_;
+    static_assert(ISSUERS == 1 || (ISSUERS == 2 && NT == 2), "one issuer, or one per tile");
     static constexpr int NBARS = NT * 5 + STAGES * 4;
     // setmaxnreg targets (warps 0-3 / softmax).  The pool is what the CTA got at launch -- 384 threads x 168
     // registers = 64512, not the whole 64K file -- and a setmaxnreg.inc that cannot be served waits forever.
@@ -288,7 +292,9 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 
     if (threadIdx.x == 0) {
         for (int t = 0; t < NT; ++t) { mbar_init(&bar_Q[t], 1); mbar_init(&bar_S[t], 1); mbar_init(&bar_Pa[t], 4); mbar_init(&bar_Pb[t], 4); mbar_init(&bar_O[t], 1); }
-        for (int s = 0; s < ST; ++s) { mbar_init(&bar_Kf[s], 1); mbar_init(&bar_Ke[s], 1); mbar_init(&bar_Vf[s], 1); mbar_init(&bar_Ve[s], 1); }
+        // "stage free" barriers: one commit per MMA issuer that is active in this CTA
+        const int n_free = C::ISSUERS == 2 ? ntiles : 1;
+        for (int s = 0; s < ST; ++s) { mbar_init(&bar_Kf[s], 1); mbar_init(&bar_Ke[s], n_free); mbar_init(&bar_Vf[s], 1); mbar_init(&bar_Ve[s], n_free); }
         fence_mbar_init();
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
     }
@@ -320,6 +326,69 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 mbar_expect_tx(&bar_Vf[s], C::KV_TILE);
                 for (int bx = 0; bx < C::BOXES; ++bx)
                     tma_load_4d(sV + s * C::KV_TILE + bx * C::KV_BOX, &tmV, &bar_Vf[s], bx * C::CPB, j * BC, hk, b, kEvictLast);
+            }
+        }
+    } else if (C::ISSUERS == 2 && (warp == 1 || warp == 3)) {
+        // ================================ MMA issuers, one per tile (experimental) =====
+        // Same MMAs and hand-offs as the single issuer below, but tile t's PV / S MMAs are issued by its own thread
+        // (warp 1: tile 0, warp 3: tile 1): a P-ready wait and the fence after it stall only that tile's issue, and
+        // the other thread keeps feeding the tensor pipe.  tcgen05.commit tracks the issuing thread's MMAs only, so
+        // the K/V "stage free" barriers take one commit from each active issuer.
+        reg_dec<C::REGS_CTRL>();
+        const int t = warp == 1 ? 0 : 1;
+        if (t < ntiles && elect_one()) {
+            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : kFmtBF16;
+            constexpr uint32_t idesc_S = make_idesc(fmt, 128, BC, false, false);
+            constexpr uint32_t idesc_PV = make_idesc(fmt, 128, D, false, true);
+            const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV);
+            const int nkv_t = (t == ntiles - 1) ? nkv : nkv_first;
+            auto issue_S = [&](int j) {
+                const int s = j % ST;
+                const uint64_t qd = make_sdesc(q_base + t * C::Q_TILE, 16, 1024, 2);
+                const uint64_t kd = make_sdesc(k_base + s * C::KV_TILE, 16, 1024, 2);
+#pragma unroll
+                for (int kk = 0; kk < D / C::KPER; ++kk) {
+                    const uint32_t inbox = (kk & 3) * 32;
+                    umma_ss<C::kF32>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
+                                     sdesc_advance(kd, (kk >> 2) * C::KV_BOX + inbox), idesc_S, kk > 0);
+                }
+                umma_commit(&bar_S[t]);
+            };
+            auto issue_PV = [&](int j, int half) {
+                const int s = j % ST;
+                const uint64_t vd = make_sdesc(v_base + s * C::KV_TILE, C::KV_BOX, C::V_SBO, C::V_LAYOUT);
+                constexpr int KH = BC / C::KPER / 2;
+#pragma unroll
+                for (int k2 = 0; k2 < KH; ++k2) {
+                    const int kk = half * KH + k2;
+                    umma_ts<C::kF32>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
+                                     sdesc_advance(vd, kk * C::KPER * 128), idesc_PV, (j > 0 || kk > 0));
+                }
+            };
+            mbar_wait(&bar_Kf[0], 0);
+            mbar_wait(&bar_Q[t], 0);
+            tc_fence_after();
+            issue_S(0);
+            umma_commit(&bar_Ke[0]);
+            for (int j = 0; j < nkv; ++j) {
+                const int s = j % ST;
+                mbar_wait(&bar_Vf[s], (j / ST) & 1);
+                if (j + 1 < nkv) mbar_wait(&bar_Kf[(j + 1) % ST], ((j + 1) / ST) & 1);
+                if (j < nkv_t) {
+                    if (C::SPLITP) {
+                        mbar_wait(&bar_Pa[t], j & 1);
+                        tc_fence_after();
+                        issue_PV(j, 0);
+                    }
+                    mbar_wait(&bar_Pb[t], j & 1);
+                    tc_fence_after();
+                    if (!C::SPLITP) issue_PV(j, 0);
+                    issue_PV(j, 1);
+                }
+                umma_commit(&bar_Ve[s]);                 // (an issuer past its own last tile has nothing pending)
+                if (j + 1 < nkv_t) issue_S(j + 1);
+                else if (j + 1 == nkv_t) umma_commit(&bar_O[t]);
+                if (j + 1 < nkv) umma_commit(&bar_Ke[(j + 1) % ST]);
             }
         }
     } else if (warp == 1) {
@@ -466,6 +535,9 @@ static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
                 if (fwd_pair_eligible(a)) return launch_fwd_pair(a, BH_valid, st);
                 return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true>>(a, BH_valid, st);
             }
+            if (variant == 4) return launch_fwd_dbuf(a, BH_valid, st);        // experimental: 64-key tiles, double-buffered S
+            if (variant == 5)                                                 // experimental: one MMA-issuing thread per tile
+                return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true, 2>>(a, BH_valid, st);
             switch (variant) {
 #define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(a, BH_valid, st);
                 B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
