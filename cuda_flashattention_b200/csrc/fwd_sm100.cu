@@ -536,6 +536,7 @@ static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
                 return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true>>(a, BH_valid, st);
             }
             if (variant == 4) return launch_fwd_dbuf(a, BH_valid, st);        // experimental: 64-key tiles, double-buffered S
+            if (variant == 6) return launch_fwd_shs(a, BH_valid, st);         // experimental: one shared score buffer, P apart
             if (variant == 5)                                                 // experimental: one MMA-issuing thread per tile
                 return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true, 2>>(a, BH_valid, st);
             switch (variant) {
