@@ -12,10 +12,21 @@
 // so S_t(j+1) is complete long before softmax_t(j) ends: the softmax warps run back to back (MUFU-bound), the MMA
 // thread only ever waits for P, and the only remaining chain is softmax(j) -> PV(j) -> S(j+2).
 // Cost: the N = 64 score MMAs are operand-fetch-bound (49 instead of 32 clk per K = 16 step, tools/mma_rate.cu), so the
-// tensor work per 128 keys and CTA grows from 2048 to ~2590 clk -- still below today's 3200-clk period.
+// tensor work per 128 keys and CTA grows from 2048 to ~2590 clk -- still below fwd_sm100.cu's 3200-clk period.
 // The O-rescale hand-off changes with it: "PV_t(j-1) is complete" can no longer be read off S_t(j)'s barrier (S_t(j)
 // is now issued BEFORE PV_t(j-1)), so every PV commits to its own barrier bar_R[t], waited for only on the (rare)
 // rescale path.
+// Two more things turned out to matter (r1(d), profiles/README.md):
+//   * ONE MMA-ISSUING THREAD PER QUERY TILE (warps 1 and 3).  With a single thread serving both tiles the kernel ran at
+//     3.95 ms: the tcgen05.fence::after_thread_sync after a P-ready wait holds the thread until its own earlier MMAs have
+//     drained, so the tensor pipe idled between the two tiles and the issuing thread fell ~1.5 steps behind the softmax
+//     warps (in-kernel trace).  With one thread per tile: 3.30 ms.
+//   * the FMA-pipe exp2 polynomial (B200_DBUF_POLY of every 16 pairs; ptx.cuh exp2_poly2).  It does not pay in
+//     fwd_sm100.cu (chain-bound), but here the softmax warps run back to back and the MUFU is the co-limiter:
+//     4 of 16 pairs -> 3.14 ms at C3 (fwd_sm100.cu: 3.28), 3.60 against 3.78 ms sustained under the power cap, causal
+//     1.71 against 1.82 ms; ncu: tensor pipe 76 % active (fwd_sm100.cu 67 %), MUFU 58 %.
+// STATUS: parity-checked against the generic kernels with tools/kbench --check (ragged, causal, N = 64 ... 8192); the
+// full pytest suite has not been run on it yet (tests/test_gpu_fwd_variants.py is that gate), so it is opt-in.
 //
 // Everything else is fwd_sm100.cu: roles, thread = row softmax with speculation and lazy rescale, P published in two
 // halves, causal / ragged masks, 4-D tensor maps (strided layouts, grouped K/V heads), epilogue through the Q tile.

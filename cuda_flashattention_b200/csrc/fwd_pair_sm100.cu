@@ -1,7 +1,7 @@
 // fwd_pair_sm100.cu -- EXPERIMENTAL forward variant (bf16, d = 128, non-causal), selected with B200_FWD_VARIANT=3:
 // the same algorithm and roles as fwd_sm100.cu, run by a CTA PAIR (cluster of 2, `tcgen05.mma.cta_group::2`).
 //
-// Why: in fwd_sm100.cu the S = Q K^T MMA (SS, M = 128, N = 128) fetches 8 KB of operands per 64
+// Why it was tried: in fwd_sm100.cu the S = Q K^T MMA (SS, M = 128, N = 128) fetches 8 KB of operands per 64
 // tensor clocks -- exactly the 128 B/clk shared-memory port -- and PV another 4 KB, while TMA writes the next K/V
 // tiles through the same port: the forward sits on the operand-fetch limit as much as on the tensor pipe.  With a CTA
 // pair every MMA is M = 256 (128 query rows in each CTA's TMEM) and the B operand is SPLIT between the two CTAs:
@@ -22,10 +22,13 @@
 //     tear-down, and each producer drains the last multicast "stage free" arrivals before its CTA may exit.
 // Shapes: Nq % 512 == 0 and Nkv % 128 == 0 (no ragged tiles, no masks) -- anything else stays on fwd_sm100.cu.
 //
-// STATUS: written at the end of round 1 after the GPU budget of the round was spent: it compiles for sm_100a and its
-// SASS has been inspected (UTCHMMA.2CTA / UTMALDG.2CTA / UTCBAR.2CTA.MULTICAST present), but it has NOT been run on
-// a B200 yet.  It is never selected by default; tools/try_fwd_variant.sh 3 is the first thing to run on a GPU box
-// (parity against the generic CUDA-core kernels, then timing against the default kernel).
+// RESULT (r1(d), profiles/r1d_fwd_pair_variant.txt): ran correctly the first time on a B200 (parity against the generic
+// kernels at N = 512 / 1024 / 4096) and is 41 % SLOWER than fwd_sm100.cu at C3 (4.69 against 3.32 ms).  The forward is
+// bound by the per-tile hand-off chain  S -> softmax -> P-ready -> PV -> S, not by operand traffic: the pair adds a
+// multicast commit and a remote mbarrier arrival to every link of that chain (about +650 clk per tile step), and halving
+// the shared-memory traffic buys nothing back.  Kept as a working reference for the cta_group::2 protocol (2-CTA TMA
+// completion on the leader's barriers, multicast commits, remote arrivals, pair-wide TMEM allocation, tear-down drain);
+// never selected by default.  tools/try_fwd_variant.sh 3 re-runs the measurement.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"

@@ -19,6 +19,12 @@
 // thread's MMAs: S-ready / K-stage-free come from warp 1, PV-done / V-stage-free / O-ready from warp 3), warp 2 owns
 // TMEM, warps 4-7 / 8-11 are the softmax warpgroups of tile 0 / 1.
 // Shapes: everything fwd_sm100.cu takes for bf16 d = 128 (ragged N, causal, strided layouts, grouped K/V heads).
+// RESULT (r1(d), profiles/r1d_fwd_shared_s_variant.txt): ran correctly the first time (parity against the generic kernels,
+// ragged and causal) and is level with fwd_sm100.cu at C3: 3.33 ms, 3.25 / 3.29 ms with 2 / 4 of 16 exponential pairs on
+// the FMA pipe (B200_SHS_POLY), against 3.28-3.32 ms.  The shared buffer is a new serial resource: every score tile
+// makes the round trip  issue -> (queue behind the PV MMAs of the in-order tensor pipe) -> 512 clk -> commit -> tcgen05.ld
+// before the OTHER tile's score MMA may even be issued, twice per 128 keys; that round trip replaces the chain it
+// removed.  (ptxas also spills the 16 speculated P registers per step at the 216-register budget.)  Kept opt-in.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.h"
