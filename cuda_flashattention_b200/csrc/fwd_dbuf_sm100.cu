@@ -18,10 +18,10 @@
 // rescale path.
 // Two more things turned out to matter (r1(d), profiles/README.md):
 //   * ONE MMA-ISSUING THREAD PER QUERY TILE (warps 1 and 3).  With a single thread serving both tiles the kernel ran at
-//     3.95 ms: in the trace the thread stands still behind every P-ready wait for about as long as its own earlier
-//     MMAs need to drain (consistent with the tcgen05.fence::after_thread_sync there waiting for them), the tensor pipe
-//     idles between the two tiles and the issuing thread falls ~1.5 steps behind the softmax warps.  With one thread
-//     per tile: 3.30 ms.
+//     3.95 ms: in the trace the tensor pipe idles between the two tiles and the issuing thread falls ~1.5 steps behind
+//     the softmax warps.  The MMA queue is shallow -- tools/mma_rate.cu prices a ready mbarrier wait between two MMA
+//     groups at ~66 clk of pipe time (the fence behind it at ~8) -- so everything one thread does between two MMAs is a
+//     pipe bubble; a second issuing thread fills it.  With one thread per tile: 3.30 ms.
 //   * the FMA-pipe exp2 polynomial (B200_DBUF_POLY of every 16 pairs; ptx.cuh exp2_poly2).  It does not pay in
 //     fwd_sm100.cu (chain-bound), but here the softmax warps run back to back and the MUFU is the co-limiter:
 //     4 of 16 pairs -> 3.14 ms at C3 (fwd_sm100.cu: 3.28), 3.60 against 3.78 ms sustained under the power cap, causal
@@ -300,10 +300,10 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
     } else if (warp == 1 || warp == 3) {
         // ================================ MMA issuers: warp 1 -> tile 0, warp 3 -> tile 1 ==================
-        // One issuing thread PER QUERY TILE.  In the r1(d) trace of the single-issuer build the thread stands still
-        // for ~340 clk behind every P-ready wait (about the drain time of its own earlier MMAs), so a single thread
-        // serving both tiles leaves the tensor pipe idle between them; with one thread per tile the other tile's
-        // MMAs fill that gap.  Commits only track the issuing thread's MMAs, so the K/V "stage free"
+        // One issuing thread PER QUERY TILE.  The MMA queue is shallow: whatever the issuing thread does between two
+        // MMAs (a ready barrier wait costs ~66 clk, tools/mma_rate.cu) is a tensor-pipe bubble, and a single thread
+        // serving both tiles fell 1.5 steps behind the softmax warps (r1(d) trace); with one thread per tile the
+        // other tile's MMAs fill the gaps.  Commits only track the issuing thread's MMAs, so the K/V "stage free"
         // barriers expect one commit from each issuer (initialised with count = ntiles).
         reg_dec<REGS_CTRL>();
         const int t = warp == 1 ? 0 : 1;

@@ -9,6 +9,10 @@ using namespace b200;
 // mode 0: SS, A K-major [128 x 128], B K-major [N x 128]        (S = Q K^T)
 // mode 1: TS, A in TMEM, B MN-major [128(k) x N]                (O += P V)
 // mode 2: alternate 8 SS + 8 TS                                 (the forward's steady state)
+// mode 3: mode 0, and after every group of 8 a wait on an mbarrier that completed long ago  (cost of a ready wait)
+// mode 4: mode 3 + tcgen05.fence::after_thread_sync behind the wait  (does the fence hold the issuing thread until its
+//         earlier MMAs have drained?  r1(d): the forward traces fit that; this prices it)
+// mode 5: mode 0 + the fence alone after every group
 __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int N, int groups, long long* out)
 {
     extern __shared__ uint8_t smem_raw[];
@@ -16,7 +20,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int N, int group
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 192 * 1024);
     uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 2);
     for (int i = threadIdx.x; i < 192 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
-    if (threadIdx.x == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+    if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); fence_mbar_init(); mbar_arrive(bar + 1); }   // bar[1]: phase 0 complete
     if (threadIdx.x < 32) { tmem_alloc<512>(slot); tmem_relinquish(); }
     fence_proxy_async_smem();
     tc_fence_before();
@@ -32,7 +36,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int N, int group
             const uint64_t vd = make_sdesc(v_base, 128 * 128, 1024, 2);
             const long long t0 = clock64();
             for (int g = 0; g < groups; ++g) {
-                if (mode == 0 || mode == 2) {
+                if (mode == 0 || mode >= 2) {
 #pragma unroll
                     for (int kk = 0; kk < 8; ++kk)
                         umma_f16_ss(tmem, sdesc_advance(ad, (kk >> 2) * 16384 + (kk & 3) * 32),
@@ -43,6 +47,8 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int N, int group
                     for (int kk = 0; kk < 8; ++kk)
                         umma_f16_ts(tmem + 256, tmem + 128 + 8 * kk, sdesc_advance(vd, kk * 2048), idesc_ts, 1);
                 }
+                if (mode == 3 || mode == 4) mbar_wait(bar + 1, 0);
+                if (mode == 4 || mode == 5) tc_fence_after();
             }
             umma_commit(bar);
             const long long t1 = clock64();
@@ -61,9 +67,10 @@ int main()
     long long* d; cudaMalloc(&d, 16);
     const int smem = 1024 + 192 * 1024 + 64;
     cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    const char* names[3] = {"SS (A,B smem K-major)", "TS (A tmem, B smem MN-major)", "8 SS + 8 TS alternating"};
+    const char* names[6] = {"SS (A,B smem K-major)", "TS (A tmem, B smem MN-major)", "8 SS + 8 TS alternating",
+                            "SS x8 + ready wait", "SS x8 + ready wait + fence", "SS x8 + fence"};
     for (int grid : {1, 148})
-        for (int mode = 0; mode < 3; ++mode)
+        for (int mode = 0; mode < 6; ++mode)
             for (int N : {64, 128, 256}) {
                 if (N == 256 && mode != 0) continue;
                 const int groups = 64;
