@@ -1,7 +1,8 @@
 // kbench.cu -- native micro-harness for the C-ABI (no Python/torch start-up): device-resident
 // N(0,1) inputs, CUDA-event timing of b200_fa2_fwd / b200_fa2_bwd, optional in-kernel trace dump
 // (library built with EXTRA=-DB200_TRACE).  Not the contract bench (that is bench.py).
-//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal] [--check]
+//   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal] [--check] [--nkv M]
+//   --nkv M: M key/value rows against N query rows (forward only; cross lengths as in the ring steps)
 //   --check: before timing, compare the forward (O, L) of the selected kernel (e.g. B200_FWD_VARIANT) with the
 //            library's generic CUDA-core kernels on the same inputs (b200_debug_force_generic); exit 5 on mismatch
 //   env B200ATTN_LIB = path of the shared object (default: cuda_flashattention_b200/libb200attn.so)
@@ -50,11 +51,14 @@ int main(int argc, char** argv)
     const char* mode = argv[1];
     const int B = atoi(argv[2]), H = atoi(argv[3]), N = atoi(argv[4]), d = atoi(argv[5]);
     const bool f32 = strcmp(argv[6], "f32") == 0;
-    int iters = 10; bool trace = false, causal = false, check = false;
+    int iters = 10, M = N; bool trace = false, causal = false, check = false;
     for (int i = 7; i < argc; ++i) {
         if (!strcmp(argv[i], "--trace")) trace = true; else if (!strcmp(argv[i], "--causal")) causal = true;
-        else if (!strcmp(argv[i], "--check")) check = true; else iters = atoi(argv[i]);
+        else if (!strcmp(argv[i], "--check")) check = true;
+        else if (!strcmp(argv[i], "--nkv") && i + 1 < argc) M = atoi(argv[++i]);
+        else iters = atoi(argv[i]);
     }
+    if (M != N && (strcmp(mode, "fwd") != 0 || causal)) { fprintf(stderr, "--nkv: forward, non-causal only\n"); return 1; }
     const char* path = getenv("B200ATTN_LIB");
     if (!path) path = "cuda_flashattention_b200/libb200attn.so";
     void* h = dlopen(path, RTLD_NOW);
@@ -67,9 +71,9 @@ int main(int argc, char** argv)
     trace_t tr = (trace_t)dlsym(h, strcmp(mode, "bwd") == 0 ? "b200_debug_trace_read_bwd" : "b200_debug_trace_read");
     if (!fwd || !bwd || !wsb || !fwdx || !bwdx) { fprintf(stderr, "missing symbols\n"); return 2; }
 
-    const size_t n = (size_t)B * H * N * d, eb = f32 ? 4 : 2;
+    const size_t n = (size_t)B * H * N * d, nk = (size_t)B * H * M * d, eb = f32 ? 4 : 2;
     void *Q, *K, *V, *O, *dO, *dQ, *dK, *dV, *ws; float* L;
-    CK(cudaMalloc(&Q, n * eb)); CK(cudaMalloc(&K, n * eb)); CK(cudaMalloc(&V, n * eb)); CK(cudaMalloc(&O, n * eb));
+    CK(cudaMalloc(&Q, n * eb)); CK(cudaMalloc(&K, nk * eb)); CK(cudaMalloc(&V, nk * eb)); CK(cudaMalloc(&O, n * eb));
     CK(cudaMalloc(&dO, n * eb)); CK(cudaMalloc(&dQ, n * eb)); CK(cudaMalloc(&dK, n * eb)); CK(cudaMalloc(&dV, n * eb));
     CK(cudaMalloc(&L, (size_t)B * H * N * 4));
     const int dt = f32 ? 1 : 0;
@@ -77,12 +81,13 @@ int main(int argc, char** argv)
     CK(cudaMalloc(&ws, wsn ? wsn : 16));
     void* bufs[4] = {Q, K, V, dO};
     for (int i = 0; i < 4; ++i) {
-        if (f32) fill_normal<float><<<148 * 8, 256>>>((float*)bufs[i], n, 1234 + i, 1.0f);
-        else fill_normal<__nv_bfloat16><<<148 * 8, 256>>>((__nv_bfloat16*)bufs[i], n, 1234 + i, 1.0f);
+        const size_t ni = (i == 1 || i == 2) ? nk : n;
+        if (f32) fill_normal<float><<<148 * 8, 256>>>((float*)bufs[i], ni, 1234 + i, 1.0f);
+        else fill_normal<__nv_bfloat16><<<148 * 8, 256>>>((__nv_bfloat16*)bufs[i], ni, 1234 + i, 1.0f);
     }
     CK(cudaDeviceSynchronize());
     const bool do_f = strcmp(mode, "bwd") != 0, do_b = strcmp(mode, "fwd") != 0;
-    auto run_f = [&]() { int s = causal ? fwdx(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 1, 0) : fwd(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 0); if (s) { fprintf(stderr, "fwd status %d\n", s); exit(3); } };
+    auto run_f = [&]() { int s = causal ? fwdx(Q, K, V, O, L, B, H, N, N, d, 0.0f, dt, 1, 0) : fwd(Q, K, V, O, L, B, H, N, M, d, 0.0f, dt, 0); if (s) { fprintf(stderr, "fwd status %d\n", s); exit(3); } };
     auto run_b = [&]() { int s = causal ? bwdx(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, 1, ws, wsn, 0)
                                           : bwd(Q, K, V, O, L, dO, dQ, dK, dV, B, H, N, N, d, 0.0f, dt, ws, wsn, 0); if (s) { fprintf(stderr, "bwd status %d\n", s); exit(3); } };
     run_f();
@@ -138,9 +143,11 @@ int main(int argc, char** argv)
     auto med = [](std::vector<float> v) { std::sort(v.begin(), v.end()); return v[v.size() / 2]; };
     auto mn = [](std::vector<float> v) { return *std::min_element(v.begin(), v.end()); };
     // causal: the visible half of the score matrix only (N (N + 1) / 2 pairs)
-    const double pairs = causal ? 0.5 * N * ((double)N + 1) : (double)N * N;
+    const double pairs = causal ? 0.5 * N * ((double)N + 1) : (double)N * M;
     const double ff = 4.0 * B * H * pairs * d, fb = 10.0 * B * H * pairs * d;
-    printf("B=%d H=%d N=%d d=%d %s%s:", B, H, N, d, f32 ? "f32" : "bf16", causal ? " causal" : "");
+    printf("B=%d H=%d N=%d", B, H, N);
+    if (M != N) printf(" Nkv=%d", M);
+    printf(" d=%d %s%s:", d, f32 ? "f32" : "bf16", causal ? " causal" : "");
     if (do_f) printf("  fwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tf), ff / med(tf) / 1e9, mn(tf), ff / mn(tf) / 1e9);
     if (do_b) printf("  bwd med %.3f ms (%.1f TF/s) best %.3f ms (%.1f)", med(tb), fb / med(tb) / 1e9, mn(tb), fb / mn(tb) / 1e9);
     printf("\n");

@@ -24,6 +24,8 @@ if [ "$V" != 3 ]; then          # the pair variant only takes full tiles, non-ca
     run B200_FWD_VARIANT=$V build/kbench fwd 1 2 1000 128 bf16 2 --check
     run B200_FWD_VARIANT=$V build/kbench fwd 1 2 1024 128 bf16 2 --check --causal
     run B200_FWD_VARIANT=$V build/kbench fwd 1 2 1472 128 bf16 2 --check --causal
+    run B200_FWD_VARIANT=$V build/kbench fwd 1 2 512 128 bf16 2 --check --nkv 2048     # cross lengths (ring steps)
+    run B200_FWD_VARIANT=$V build/kbench fwd 1 2 1000 128 bf16 2 --check --nkv 200
 fi
 run B200_FWD_VARIANT=$V build/kbench fwd 2 4 4096 128 bf16 3 --check
 run B200_FWD_VARIANT=1 build/kbench fwd 8 16 8192 128 bf16 10
