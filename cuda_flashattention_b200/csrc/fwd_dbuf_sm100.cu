@@ -217,7 +217,9 @@ __device__ __forceinline__ void dbuf_softmax_role(int t, uint32_t tmem, uint8_t*
         Lout[(size_t)bh * ldL + row] = (m + log2f(l)) * 0.6931471805599453f;
 }
 
-template <int POLY>
+// PEEL (B200_DBUF_PEEL=1, NOT yet run on a GPU): the issuers' steady-state iterations without any data-dependent branch
+// between two runs of MMAs (see the note at the loop).  PEEL = false is the build all r1(d) measurements were taken on.
+template <int POLY, bool PEEL>
 __global__ void __launch_bounds__(fdb::THREADS, 1)
 fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -344,7 +346,30 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (jj < nkv_t) issue_S(jj);
                 umma_commit(&bar_Ke[jj]);
             }
-            for (int j = 0; j < nkv; ++j) {
+            int j0 = 0;
+            if constexpr (PEEL) {
+                // Steady state (j + 2 < nkv_t): every decision of the general loop below is known.  tools/mma_rate.cu shows
+                // that whatever the issuing thread executes between two tcgen05.mma -- a ready barrier wait (~66 clk), even
+                // the loop's own compares and branches -- turns into a tensor-pipe bubble, so these iterations carry
+                // nothing but the four barrier waits.
+                for (; j0 + 2 < nkv_t; ++j0) {
+                    const int j = j0, s = j % ST, u = j & 1;
+                    const uint32_t ph = (j >> 1) & 1;
+                    mbar_wait(&bar_Vf[s], (j / ST) & 1);
+                    mbar_wait(&bar_Kf[(j + 2) % ST], ((j + 2) / ST) & 1);
+                    mbar_wait(&bar_Pa[2 * t + u], ph);
+                    tc_fence_after();
+                    issue_PV(j, 0);
+                    mbar_wait(&bar_Pb[2 * t + u], ph);
+                    tc_fence_after();
+                    issue_PV(j, 1);
+                    umma_commit(&bar_R[t]);
+                    umma_commit(&bar_Ve[s]);
+                    issue_S(j + 2);
+                    umma_commit(&bar_Ke[(j + 2) % ST]);
+                }
+            }
+            for (int j = j0; j < nkv; ++j) {
                 const int s = j % ST, u = j & 1;
                 const uint32_t ph = (j >> 1) & 1;
                 if (t == 0) FDB_TR(2, j, 0);
@@ -401,7 +426,7 @@ int dbuf_trace_read(long long* out, int n)
 }
 #endif
 
-template <int POLY>
+template <int POLY, bool PEEL = false>
 static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
     using namespace fdb;
@@ -409,7 +434,7 @@ static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(fwd_dbuf_kernel<POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(fwd_dbuf_kernel<POLY, PEEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -421,7 +446,7 @@ static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
         make_tmap_4d(&tmO, a.O, dt, 2, a.B, a.H, a.Nq, D, a.lo.sb, a.lo.sh, a.lo.sn, 128, 64))
         return B200_ERR_CUDA;
     dim3 grid((a.Nq + NT * 128 - 1) / (NT * 128), a.H, a.B);
-    fwd_dbuf_kernel<POLY><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
+    fwd_dbuf_kernel<POLY, PEEL><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
                                                        a.H / a.Hkv, BH_valid);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
@@ -433,6 +458,13 @@ int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st)
     if (a.dtype != B200_DTYPE_BF16 || a.d != fdb::D) return B200_ERR_UNSUPPORTED;
     static int poly = -1;                                // tuning hook: B200_DBUF_POLY = pairs of every 16 on the FMA pipe
     if (poly < 0) { const char* e = getenv("B200_DBUF_POLY"); poly = e ? atoi(e) : 0; }
+    static int peel = -1;                                // untested hook: B200_DBUF_PEEL=1 (with POLY 0 or 4)
+    if (peel < 0) { const char* e = getenv("B200_DBUF_PEEL"); peel = e ? atoi(e) : 0; }
+    if (peel) {
+        if (poly == 0) return launch_fwd_dbuf_t<0, true>(a, BH_valid, st);
+        if (poly == 4) return launch_fwd_dbuf_t<4, true>(a, BH_valid, st);
+        return B200_ERR_UNSUPPORTED;
+    }
     switch (poly) {
         case 0: return launch_fwd_dbuf_t<0>(a, BH_valid, st);
         case 3: return launch_fwd_dbuf_t<3>(a, BH_valid, st);

@@ -24,6 +24,7 @@ MODULES = ["tests/test_gpu_fwd_tc.py", "tests/test_gpu_causal.py", "tests/test_g
 VARIANTS = [
     ("4", {"B200_DBUF_POLY": "4"}),     # 64-key tiles, double-buffered scores, one issuer per tile, 4/16 exp2 on the FMA pipe
     ("4", {"B200_DBUF_POLY": "0"}),
+    ("4", {"B200_DBUF_POLY": "4", "B200_DBUF_PEEL": "1"}),   # + branch-free steady-state issue loops (never run on a GPU yet)
     ("6", {"B200_SHS_POLY": "0"}),      # one shared score buffer, P in its own TMEM columns
     ("3", {}),                          # CTA pairs (full tiles only; other shapes fall back to the default kernel)
     ("5", {}),                          # default kernel with one issuer per tile
