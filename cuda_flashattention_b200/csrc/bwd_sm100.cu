@@ -30,6 +30,7 @@
 #include "ptx.cuh"
 #include "tmap.h"
 #include <stdlib.h>
+#include <type_traits>
 
 namespace b200 {
 
@@ -283,7 +284,11 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 // DR = real head dimension (128 or 64).  The tile layout is the d = 128 one; for d = 64 only the first 64-wide box of
 // every tile is loaded and the MMAs run over 64 (M1, M2: K extent; M3, M4: N extent).  M5 has d as its M extent, which
 // stays 128: the second box of K is zero-filled once, so lanes 64..127 of dQ^T are zero and are not drained.
-template <int DR>
+// ISSUE = 1 (B200_BWD_VARIANT=1, d = 128 only; built, NOT yet run on a GPU): the MMA thread's steady state unrolled by
+// six iterations (the period of the 2 S buffers and the 3 Q/dO stages) so that buffer, stage and most phase choices are
+// compile-time constants, and the dQ-columns-free wait taken together with the dS wait -- tools/mma_rate.cu shows that
+// whatever the issuing thread executes between two tcgen05.mma (a ready barrier wait: ~66 clk) is a tensor-pipe bubble.
+template <int DR, int ISSUE = 0>
 __global__ void __launch_bounds__(bwd::THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -401,7 +406,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
             mbar_wait(&bar_in_full[0], 0);
             tc_fence_after();
             M1(0); M2(0);
-            for (int i = 0; i < n_tot; ++i) {
+            auto gen = [&](const int i) {                       // one iteration, everything decided at run time
                 const int b = i & 1, s = i % NS;
                 if (i + 1 < n_tot) {
                     mbar_wait(&bar_in_full[(i + 1) % NS], ((i + 1) / NS) & 1);
@@ -433,6 +438,48 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 }
                 umma_commit(bar_dQ_full);
                 B200_TRB(2, i, 6);
+            };
+            if constexpr (ISSUE == 1) {
+                // one steady-state iteration i = 6 k + c (i > 0, i + 1 < n_tot): b = c & 1, s = c % 3 and every barrier
+                // parity except bar_P's (which also depends on k & 1 = kp) are constants
+                auto step = [&](auto c_tag, const uint32_t kp) {
+                    constexpr int c = decltype(c_tag)::value;
+                    constexpr int b = c & 1, s = c % NS, s1 = (c + 1) % NS, b1 = (c + 1) & 1;
+                    mbar_wait(&bar_in_full[s1], ((c + 1) / NS) & 1);
+                    tc_fence_after();
+                    mma_ss(sb + OFF_K, sb + OFF_Q + s1 * Q_TILE, TM_S + 64 * b1);           // M1(i + 1)
+                    umma_commit(&bar_S[b1]);
+                    mbar_wait(&bar_P[b], kp ^ ((c >> 1) & 1));
+                    tc_fence_after();
+                    mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, true);           // M3
+                    mbar_wait(bar_dS, c & 1);
+                    mbar_wait(bar_dQ_empty, (c & 1) ^ 1);                                    // (usually long since free)
+                    tc_fence_after();
+                    mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, true);                    // M4
+                    umma_commit(&bar_in_empty[s]);
+                    mma_ss(sb + OFF_V, sb + OFF_DO + s1 * Q_TILE, TM_DP);                   // M2(i + 1)
+                    umma_commit(bar_dP);
+                    {                                                                       // M5
+                        const uint64_t ad = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
+                        const uint64_t bd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
+#pragma unroll
+                        for (int kk = 0; kk < BN / 16; ++kk)
+                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(ad, kk * 2048), sdesc_advance(bd, kk * 2048), idesc_dq, kk > 0);
+                    }
+                    umma_commit(bar_dQ_full);
+                };
+                int i = 0;
+                const int head = n_tot < 6 ? n_tot : 6;
+                for (; i < head; ++i) gen(i);                    // (i = 0 does not accumulate into dV / dK)
+                for (; i + 6 < n_tot; i += 6) {                  // i is a multiple of 6; the block's last iteration has a successor
+                    const uint32_t kp = (uint32_t)(i / 6) & 1u;
+                    step(std::integral_constant<int, 0>{}, kp); step(std::integral_constant<int, 1>{}, kp);
+                    step(std::integral_constant<int, 2>{}, kp); step(std::integral_constant<int, 3>{}, kp);
+                    step(std::integral_constant<int, 4>{}, kp); step(std::integral_constant<int, 5>{}, kp);
+                }
+                for (; i < n_tot; ++i) gen(i);
+            } else {
+                for (int i = 0; i < n_tot; ++i) gen(i);
             }
             umma_commit(bar_done);
         }
@@ -533,7 +580,7 @@ struct BwdLaunch {
     int stat_stride = 0, dq_rows = 0;    // floats per slab of L2p / Dp and rows per slab of dQacc; 0 = pad64(Nq) / Nq
 };
 
-template <int DR>
+template <int DR, int ISSUE = 0>
 static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 {
     using namespace bwd;
@@ -542,7 +589,7 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR, ISSUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int Nq_pad = (a.Nq + 63) / 64 * 64, Hq = a.Hkv * a.G;
@@ -559,12 +606,20 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     // experiment hook, timing only (wrong dQ): B200_BWD_DBG bit 0 skips the dQ reduce-adds, bit 1 issues plain stores instead
     static int dbg = -1;
     if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 3) : 0; }
-    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
+    bwd_kernel<DR, ISSUE><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
                                                 a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
                                                 a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
+}
+
+// B200_BWD_VARIANT=1 selects the experimental issue loop (bwd_kernel<128, 1>); d = 64 always runs the measured one
+static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st)
+{
+    static int variant = -1;
+    if (variant < 0) { const char* e = getenv("B200_BWD_VARIANT"); variant = e ? atoi(e) : 0; }
+    return variant == 1 ? bwd_launch<128, 1>(a, st) : bwd_launch<128>(a, st);
 }
 
 // contiguous [BH, N, 128 or 64] slabs (the reference layout); BH is cut into (batches x heads) that fit the grid limits
@@ -594,7 +649,7 @@ static int bwd_run(const BwdLaunch& a, int BHq, int d, void* ws, void* dQ, const
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
     BwdLaunch b = a;
     b.L2p = L2p; b.Dp = Dp; b.dQacc = dQacc;
-    if (d == 128) B200_TRY(bwd_launch<128>(b, st)); else B200_TRY(bwd_launch<64>(b, st));
+    if (d == 128) B200_TRY(bwd_launch_d128(b, st)); else B200_TRY(bwd_launch<64>(b, st));
     if (ldq == nullptr) {
         unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
         if (cgrid > 148u * 8) cgrid = 148u * 8;
@@ -684,7 +739,7 @@ int tc_bwd_ring_step_sub(const void* Q, const void* K, const void* V, const void
     a.lq = a.ldo = a.lk = a.lv = a.ldk = a.ldv = full;
     a.stat_stride = Nl_pad;
     a.dq_rows = Nl;
-    return bwd_launch<128>(a, st);
+    return bwd_launch_d128(a, st);
 }
 
 }  // namespace b200

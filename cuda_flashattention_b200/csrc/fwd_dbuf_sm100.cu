@@ -27,7 +27,7 @@
 //     4 of 16 pairs -> 3.14 ms at C3 (fwd_sm100.cu: 3.28), 3.60 against 3.78 ms sustained under the power cap, causal
 //     1.71 against 1.82 ms; ncu: tensor pipe 76 % active (fwd_sm100.cu 67 %), MUFU 58 %.
 // STATUS: parity-checked against the generic kernels with tools/kbench --check (ragged, causal, N = 64 ... 8192); the
-// full pytest suite has not been run on it yet (tests/test_gpu_fwd_variants.py is that gate), so it is opt-in.
+// full pytest suite has not been run on it yet (tests/test_gpu_kernel_variants.py is that gate), so it is opt-in.
 //
 // Everything else is fwd_sm100.cu: roles, thread = row softmax with speculation and lazy rescale, P published in two
 // halves, causal / ragged masks, 4-D tensor maps (strided layouts, grouped K/V heads), epilogue through the Q tile.

@@ -1,4 +1,6 @@
 #!/bin/bash
+# Gate for promoting an experimental forward kernel (for the backward variant: B200_BWD_VARIANT=1 with the modules of
+# tests/test_gpu_kernel_variants.py BWD_MODULES)
 # Gate for promoting an experimental forward kernel to the default: the forward-facing GPU parity
 # suite under the variant, then the contract bench and an ncu launch list with the variant selected through the
 # environment.  One gpurun call, about 10 GPU-minutes:
