@@ -1,9 +1,8 @@
 #!/bin/bash
-# Gate for promoting an experimental forward kernel (for the backward variant: B200_BWD_VARIANT=1 with the modules of
-# tests/test_gpu_kernel_variants.py BWD_MODULES)
 # Gate for promoting an experimental forward kernel to the default: the forward-facing GPU parity
 # suite under the variant, then the contract bench and an ncu launch list with the variant selected through the
-# environment.  One gpurun call, about 10 GPU-minutes:
+# environment.  (The backward's B200_BWD_VARIANT=1 goes through tests/test_gpu_kernel_variants.py the same way.)
+# One gpurun call, about 10 GPU-minutes:
 #   gpurun --timeout 900 -- 'bash tools/promote_fwd_variant.sh'
 # If everything is green, make the variant the default in dispatch_fwd (csrc/fwd_sm100.cu: `variant = e ? atoi(e) : 1`)
 # and commit the new bench line / launch list under profiles/.
