@@ -118,6 +118,7 @@ struct HostPipe {
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     void* buf = nullptr;
     size_t bytes = 0;
+    bool ready = false;                          // every stream / event above exists
 };
 static HostPipe g_pipe[64];
 static std::mutex g_pipe_mu;
@@ -135,17 +136,18 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
     B200_CUDA_TRY(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lk(g_pipe_mu);
     HostPipe& P = g_pipe[dev];
-    if (!P.h2d) {
-        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.h2d, cudaStreamNonBlocking));
-        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.comp, cudaStreamNonBlocking));
-        B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.d2h, cudaStreamNonBlocking));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_start, cudaEventDisableTiming));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_end, cudaEventDisableTiming));
+    if (!P.ready) {                              // (a failed creation is retried by the next call, never run with null handles)
+        if (!P.h2d) B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.h2d, cudaStreamNonBlocking));
+        if (!P.comp) B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.comp, cudaStreamNonBlocking));
+        if (!P.d2h) B200_CUDA_TRY(cudaStreamCreateWithFlags(&P.d2h, cudaStreamNonBlocking));
+        if (!P.ev_start) B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_start, cudaEventDisableTiming));
+        if (!P.ev_end) B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_end, cudaEventDisableTiming));
         for (int i = 0; i < 2; ++i) {
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_in[i], cudaEventDisableTiming));
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_done[i], cudaEventDisableTiming));
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_out[i], cudaEventDisableTiming));
+            if (!P.ev_in[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_in[i], cudaEventDisableTiming));
+            if (!P.ev_done[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_done[i], cudaEventDisableTiming));
+            if (!P.ev_out[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&P.ev_out[i], cudaEventDisableTiming));
         }
+        P.ready = true;
     }
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t slab = (size_t)N * d * es, lslab = (size_t)N * sizeof(float);

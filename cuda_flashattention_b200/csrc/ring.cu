@@ -37,6 +37,7 @@ struct RingState {
     cudaEvent_t ev_attn[2] = {nullptr, nullptr}, ev_merge[2] = {nullptr, nullptr};        // next step's CTAs fill the SMs the current step's last wave leaves idle
     void* buf = nullptr;                    // cached scratch
     size_t bytes = 0;
+    bool ready = false;                     // every stream / event above exists
 };
 static RingState g_ring[64];
 static std::mutex g_ring_mu;
@@ -48,17 +49,20 @@ static int ring_state(RingState** out)
     if (dev < 0 || dev >= 64) return B200_ERR_INVALID_ARGUMENT;
     std::lock_guard<std::mutex> lk(g_ring_mu);
     RingState& s = g_ring[dev];
-    if (!s.comm_stream) {
-        B200_CUDA_TRY(cudaStreamCreateWithFlags(&s.comm_stream, cudaStreamNonBlocking));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_main, cudaEventDisableTiming));
-        B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_acc, cudaEventDisableTiming));
+    if (!s.ready) {
+        // (a failed creation leaves `ready` false: the next call retries what is still missing instead of running
+        // with null handles)
+        if (!s.comm_stream) B200_CUDA_TRY(cudaStreamCreateWithFlags(&s.comm_stream, cudaStreamNonBlocking));
+        if (!s.ev_main) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_main, cudaEventDisableTiming));
+        if (!s.ev_acc) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_acc, cudaEventDisableTiming));
         for (int i = 0; i < 2; ++i) {
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_comm[i], cudaEventDisableTiming));
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_compute[i], cudaEventDisableTiming));
-            B200_CUDA_TRY(cudaStreamCreateWithFlags(&s.attn_stream[i], cudaStreamNonBlocking));
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_attn[i], cudaEventDisableTiming));
-            B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_merge[i], cudaEventDisableTiming));
+            if (!s.ev_comm[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_comm[i], cudaEventDisableTiming));
+            if (!s.ev_compute[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_compute[i], cudaEventDisableTiming));
+            if (!s.attn_stream[i]) B200_CUDA_TRY(cudaStreamCreateWithFlags(&s.attn_stream[i], cudaStreamNonBlocking));
+            if (!s.ev_attn[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_attn[i], cudaEventDisableTiming));
+            if (!s.ev_merge[i]) B200_CUDA_TRY(cudaEventCreateWithFlags(&s.ev_merge[i], cudaEventDisableTiming));
         }
+        s.ready = true;
     }
     *out = &s;
     return B200_OK;
