@@ -200,7 +200,12 @@ B200_API int b200_ring_kv_block(int rank, int step, int nranks);
  *   src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:143-239, with
  *   ring_exchange_kv (src/util/nccl_utils.h:133-142) on an internal side stream.
  * Batched: local shards are [B,H,N_local,d]; L_local is [B,H,N_local] (LSE).  K_local/V_local are
- * NOT modified (the reference overwrites them for nranks >= 3).  nranks == 1 needs no communicator. */
+ * NOT modified (the reference overwrites them for nranks >= 3).  nranks == 1 needs no communicator.
+ * The ring calls are COLLECTIVE: every rank of `comm` makes the same sequence of ring calls with the same shapes (the
+ * copy-engine transport counts on it -- its hand-off counters are derived from the call sequence, and its scratch is
+ * re-exported collectively when a call needs a larger one).  If a ring call returns an error on any rank, the
+ * transport state of that communicator is undefined: destroy it (b200_ring_comm_destroy) and create a new one before
+ * the next ring call, as one would after a failed NCCL collective. */
 B200_API int b200_ring_fwd(const void* Q_local, const void* K_local, const void* V_local, void* O_local, float* L_local,
                   int B, int H, int N_local, int d, float scale, int dtype,
                   ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
