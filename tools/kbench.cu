@@ -3,8 +3,9 @@
 // (library built with EXTRA=-DB200_TRACE).  Not the contract bench (that is bench.py).
 //   kbench <fwd|bwd|both> B H N d <bf16|f32> [iters] [--trace] [--causal] [--check] [--nkv M]
 //   --nkv M: M key/value rows against N query rows (forward only; cross lengths as in the ring steps)
-//   --check: before timing, compare the forward (O, L) of the selected kernel (e.g. B200_FWD_VARIANT) with the
-//            library's generic CUDA-core kernels on the same inputs (b200_debug_force_generic); exit 5 on mismatch
+//   --check: before timing, compare the forward (O, L) of the selected kernel (e.g. B200_FWD_VARIANT) -- and with
+//            bwd / both the gradients (e.g. B200_BWD_VARIANT) -- with the library's generic CUDA-core kernels on the
+//            same inputs (b200_debug_force_generic); exit 5 on mismatch
 //   env B200ATTN_LIB = path of the shared object (default: cuda_flashattention_b200/libb200attn.so)
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
@@ -123,6 +124,34 @@ int main(int argc, char** argv)
                ok ? "PASS" : "FAIL");
         if (!ok) return 5;
         run_f();
+        if (do_b) {
+            // backward parity on the same (O, L): selected kernel (e.g. B200_BWD_VARIANT) against the generic kernels
+            run_b();
+            CK(cudaDeviceSynchronize());
+            void* g[3] = {dQ, dK, dV};
+            std::vector<uint8_t> g1[3], g2[3];
+            for (int t = 0; t < 3; ++t) { g1[t].resize(n * eb); g2[t].resize(n * eb); CK(cudaMemcpy(g1[t].data(), g[t], n * eb, cudaMemcpyDeviceToHost)); }
+            force(1); run_b(); force(0);
+            CK(cudaDeviceSynchronize());
+            const char* names[3] = {"dQ", "dK", "dV"};
+            bool okb = true;
+            for (int t = 0; t < 3; ++t) {
+                CK(cudaMemcpy(g2[t].data(), g[t], n * eb, cudaMemcpyDeviceToHost));
+                double mx = 0, num2 = 0, den2 = 0, ref_max = 1.0; size_t bad2 = 0;   // (N(0,1) dO: gradients are not unit-scale)
+                for (size_t i = 0; i < n; ++i) {
+                    const double a = val(g1[t], i), b = val(g2[t], i), e = fabs(a - b);
+                    if (!(e <= 1e30)) ++bad2;
+                    if (e > mx) mx = e;
+                    if (fabs(b) > ref_max) ref_max = fabs(b);
+                    num2 += e * e; den2 += b * b;
+                }
+                const double rel2 = sqrt(num2 / (den2 > 0 ? den2 : 1));
+                const bool o = bad2 == 0 && mx <= tol * ref_max && rel2 <= 1e-2;
+                printf("check %s vs generic kernels: max|d| %.3e  rel-L2 %.3e  non-finite %zu  -> %s\n", names[t], mx, rel2, bad2, o ? "PASS" : "FAIL");
+                okb = okb && o;
+            }
+            if (!okb) return 5;
+        }
     }
     for (int i = 0; i < 3; ++i) { if (do_f) run_f(); if (do_b) run_b(); }
     CK(cudaDeviceSynchronize());
