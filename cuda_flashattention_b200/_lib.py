@@ -69,6 +69,7 @@ _SIGS = {
     "b200_ring_bwd_ex": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
     "b200_ring_zigzag_chunk": (_i, [_i, _i, _i]),
     "b200_ring_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
+    "b200_ring_set_transport": (_i, [_i]),
     "b200_ring_unique_id": (_i, [_vp]),
     "b200_ring_comm_init": (_i, [C.POINTER(C.c_void_p), _vp, _i, _i]),
     "b200_ring_comm_destroy": (_i, [_vp]),

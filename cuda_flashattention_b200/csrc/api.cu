@@ -234,8 +234,8 @@ namespace b200 { int fwd_trace_read(long long* out, int n); int bwd_trace_read(l
 extern "C" {
 __attribute__((visibility("default"))) int b200_debug_trace_read(long long* out, int n)
 {
-    const char* e = getenv("B200_FWD_VARIANT");           // the experimental double-buffered forward keeps its own trace
-    return (e && atoi(e) == 4) ? b200::dbuf_trace_read(out, n) : b200::fwd_trace_read(out, n);
+    const char* e = getenv("B200_FWD_VARIANT");           // the double-buffered forward (the default) keeps its own trace
+    return (!e || atoi(e) == 4) ? b200::dbuf_trace_read(out, n) : b200::fwd_trace_read(out, n);
 }
 __attribute__((visibility("default"))) int b200_debug_trace_read_bwd(long long* out, int n) { return b200::bwd_trace_read(out, n); }
 #endif

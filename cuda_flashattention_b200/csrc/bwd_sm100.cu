@@ -65,6 +65,15 @@ constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DQ = 192, TM_DV = 256, TM_DK = 384;
 #ifdef B200_TRACE
 __device__ long long g_trace_bwd[3 * 8 * 8];
 #endif
+// Timing-only experiment hooks (WRONG RESULTS): compiled only into `make VARIANT=exp EXTRA=-DB200_EXPERIMENTS` side
+// libraries, selected there by B200_BWD_DBG; the product build folds every B200_DBG(...) to false.
+//   1 no dQ staging / reduction   2 plain dQ stores (B200_DQ_RED build)   4 no M5   8 no dS shared-memory copy
+//   16 no M1   32 no M2   64 no M3 / M4   128 no exponentials
+#ifdef B200_EXPERIMENTS
+#define B200_DBG(bit) ((dbg & (bit)) != 0)
+#else
+#define B200_DBG(bit) false
+#endif
 // roles: 0 = compute warpgroup 0 (its warp 0), 1 = dQ drain warpgroup (its warp 0), 2 = MMA issuer
 #define B200_TRB(role, i, ev) B200_TRACE_EVENT(g_trace_bwd, role, i, ev, (role) == 2 || (((threadIdx.x >> 5) & 3) == 0 && ((role) == 1 || threadIdx.x < 256)))
 
@@ -92,8 +101,9 @@ __device__ __forceinline__ void red_add_f32(float* gaddr, float v) {
 __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* smem, uint64_t* bar_in_full,
                                                  uint64_t* bar_S, uint64_t* bar_dP, uint64_t* bar_P, uint64_t* bar_dS,
                                                  int n_tot, int n_it, int qt_min, int i_off, int kv0, int causal,
-                                                 float scale_log2, float scale)
+                                                 float scale_log2, float scale, int dbg)
 {
+    (void)dbg;
     using namespace bwd;
     const int r = threadIdx.x & 127;                                   // kv row within the tile == TMEM lane
     const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
@@ -117,7 +127,8 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         B200_TRB(0, i, 4);
         float p[32];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
+        for (int c = 0; c < 32; ++c)
+            p[c] = B200_DBG(128) ? fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]) : fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
         if (causal) {
             // key kv0 + r is hidden from the queries before it: only the two q tiles on the diagonal are affected
             int qt = ii + i_off;
@@ -159,9 +170,11 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
         B200_TMEM_ST_16(tP, dk);
         // smem copy (B operand of M5): row r = 128 B, this warpgroup owns 16-byte chunks 4w..4w+3
         uint8_t* rowp = smem + OFF_DS + b * DS_TILE + r * 128;
+        if (!B200_DBG(8)) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            *reinterpret_cast<uint4*>(rowp + (((4 * w + q) ^ (r & 7)) * 16)) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+            for (int q = 0; q < 4; ++q)
+                *reinterpret_cast<uint4*>(rowp + (((4 * w + q) ^ (r & 7)) * 16)) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
+        }
         fence_proxy_async_smem();
         tmem_wait_st();
         tc_fence_before();
@@ -183,6 +196,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
                                                int i_off, size_t bhq0, int dbg, uint8_t* smem)
 {
     using namespace bwd;
+    (void)dbg;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
     const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
     const bool lane0 = (threadIdx.x & 31) == 0;
@@ -206,7 +220,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
         float* dst = dQacc + (bh * dq_rows + (size_t)qt * BM) * DR + r;   // (dq_rows: rows per slab of the accumulator)
         const int q_valid = min(BM, Nq - qt * BM);                     // ragged last q tile: rows past Nq do not exist
 #ifndef B200_DQ_RED
-        if (!(dbg & 1)) {
+        if (!B200_DBG(1)) {
             const bool leader = (threadIdx.x & 127) == 0;
 #pragma unroll
             for (int half = 0; half < BM / STG_ROWS; ++half) {
@@ -227,8 +241,8 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
             }
         }
 #else
-        if (!(dbg & 1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
-            if (dbg & 2) {                                             // experiment: plain stores, same bytes, no L2 atomic
+        if (!B200_DBG(1) && r < DR) {                                    // (d = 64: lanes 64..127 hold the zero padding)
+            if (B200_DBG(2)) {                                             // experiment: plain stores, same bytes, no L2 atomic
 #pragma unroll
                 for (int q = 0; q < BM; ++q) dst[q * DR] = __uint_as_float(v[q]);
             } else if (q_valid == BM) {
@@ -284,10 +298,9 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 // DR = real head dimension (128 or 64).  The tile layout is the d = 128 one; for d = 64 only the first 64-wide box of
 // every tile is loaded and the MMAs run over 64 (M1, M2: K extent; M3, M4: N extent).  M5 has d as its M extent, which
 // stays 128: the second box of K is zero-filled once, so lanes 64..127 of dQ^T are zero and are not drained.
-// ISSUE = 1 (B200_BWD_VARIANT=1, d = 128 only; built, NOT yet run on a GPU): the MMA thread's steady state unrolled by
-// six iterations (the period of the 2 S buffers and the 3 Q/dO stages) so that buffer, stage and most phase choices are
-// compile-time constants, and the dQ-columns-free wait taken together with the dS wait -- tools/mma_rate.cu shows that
-// whatever the issuing thread executes between two tcgen05.mma (a ready barrier wait: ~66 clk) is a tensor-pipe bubble.
+// ISSUE selects the MMA thread's issue order: 0 = one MMA group after the other, 2 = SS / TS interleaved (see the loop).
+// (r2: an unrolled-by-six issue loop with merged waits, "ISSUE = 1", measured 4-5 % SLOWER at C3 and was removed:
+// profiles/r2a_bwd_variant1_negative.txt.)
 template <int DR, int ISSUE = 0>
 __global__ void __launch_bounds__(bwd::THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -399,8 +412,8 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                     umma_f16_ts(tmem + d_col, tmem + a_col + (kk < 2 ? 8 * kk : 32 + 8 * (kk - 2)),
                                 sdesc_advance(bd, kk * 2048), idesc_ts, (acc || kk > 0) ? 1u : 0u);
             };
-            auto M1 = [&](int i) { mma_ss(sb + OFF_K, sb + OFF_Q + (i % NS) * Q_TILE, TM_S + 64 * (i & 1)); umma_commit(&bar_S[i & 1]); };
-            auto M2 = [&](int i) { mma_ss(sb + OFF_V, sb + OFF_DO + (i % NS) * Q_TILE, TM_DP); umma_commit(bar_dP); };
+            auto M1 = [&](int i) { if (!B200_DBG(16)) mma_ss(sb + OFF_K, sb + OFF_Q + (i % NS) * Q_TILE, TM_S + 64 * (i & 1)); umma_commit(&bar_S[i & 1]); };
+            auto M2 = [&](int i) { if (!B200_DBG(32)) mma_ss(sb + OFF_V, sb + OFF_DO + (i % NS) * Q_TILE, TM_DP); umma_commit(bar_dP); };
 
             mbar_wait(bar_KV, 0);
             mbar_wait(&bar_in_full[0], 0);
@@ -417,19 +430,19 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 mbar_wait(&bar_P[b], (i >> 1) & 1);
                 tc_fence_after();
                 B200_TRB(2, i, 1);
-                mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, i > 0);          // M3: dV += P^T dO_i
+                if (!B200_DBG(64)) mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, i > 0);          // M3: dV += P^T dO_i
                 B200_TRB(2, i, 2);
                 mbar_wait(bar_dS, i & 1);
                 tc_fence_after();
                 B200_TRB(2, i, 3);
-                mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
+                if (!B200_DBG(64)) mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, i > 0);                   // M4: dK += dS^T Q_i
                 umma_commit(&bar_in_empty[s]);
                 if (i + 1 < n_tot) M2(i + 1);
                 B200_TRB(2, i, 4);
                 mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
                 tc_fence_after();
                 B200_TRB(2, i, 5);
-                {                                                                       // M5: dQ_i^T = K^T dS
+                if (!B200_DBG(4)) {                                                     // M5: dQ_i^T = K^T dS
                     const uint64_t ad = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
                     const uint64_t bd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
 #pragma unroll
@@ -439,45 +452,72 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 umma_commit(bar_dQ_full);
                 B200_TRB(2, i, 6);
             };
-            if constexpr (ISSUE == 1) {
-                // one steady-state iteration i = 6 k + c (i > 0, i + 1 < n_tot): b = c & 1, s = c % 3 and every barrier
-                // parity except bar_P's (which also depends on k & 1 = kp) are constants
-                auto step = [&](auto c_tag, const uint32_t kp) {
-                    constexpr int c = decltype(c_tag)::value;
-                    constexpr int b = c & 1, s = c % NS, s1 = (c + 1) % NS, b1 = (c + 1) & 1;
-                    mbar_wait(&bar_in_full[s1], ((c + 1) / NS) & 1);
-                    tc_fence_after();
-                    mma_ss(sb + OFF_K, sb + OFF_Q + s1 * Q_TILE, TM_S + 64 * b1);           // M1(i + 1)
-                    umma_commit(&bar_S[b1]);
-                    mbar_wait(&bar_P[b], kp ^ ((c >> 1) & 1));
-                    tc_fence_after();
-                    mma_ts(TM_S + 64 * b, sb + OFF_DO + s * Q_TILE, TM_DV, true);           // M3
-                    mbar_wait(bar_dS, c & 1);
-                    mbar_wait(bar_dQ_empty, (c & 1) ^ 1);                                    // (usually long since free)
-                    tc_fence_after();
-                    mma_ts(TM_DP, sb + OFF_Q + s * Q_TILE, TM_DK, true);                    // M4
-                    umma_commit(&bar_in_empty[s]);
-                    mma_ss(sb + OFF_V, sb + OFF_DO + s1 * Q_TILE, TM_DP);                   // M2(i + 1)
-                    umma_commit(bar_dP);
-                    {                                                                       // M5
-                        const uint64_t ad = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
-                        const uint64_t bd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
-#pragma unroll
-                        for (int kk = 0; kk < BN / 16; ++kk)
-                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(ad, kk * 2048), sdesc_advance(bd, kk * 2048), idesc_dq, kk > 0);
-                    }
-                    umma_commit(bar_dQ_full);
+            if constexpr (ISSUE == 2) {
+                // Interleaved issue order.  A lone run of N = 64 SS MMAs is operand-fetch-bound (6 KB of shared memory per
+                // 32 clk of math; tools/mma_rate.cu: ~46-63 clk each), a TS MMA with N = 128 is not (4 KB per 64 clk), and
+                // the fetch of an SS MMA overlaps the math of the TS MMA ahead of it (the probe's alternating case).  So
+                // the 24 SS and 8 TS MMAs of an iteration are issued as SS SS TS triples wherever the TMEM hazards allow:
+                //   G1 = M1(i+1) x M3(i)   (S[(i+1)&1] written, P^T in S[i&1] read: different buffers)
+                //   G2 = M5(i)   x M4(i)   (dQ columns written, dS^T in the dP columns read)
+                //   G3 = M2(i+1)           (overwrites the dP columns M4(i) reads: has to follow it)
+                // which also leaves two barrier waits per iteration instead of four.
+                const uint64_t k_kmaj = make_sdesc(sb + OFF_K, 16, 1024, 2), v_kmaj = make_sdesc(sb + OFF_V, 16, 1024, 2);
+                const uint64_t k_mnmaj = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
+                auto ss_step = [&](uint64_t ad, uint64_t bd, uint32_t d_col, int kk) {
+                    umma_f16_ss(tmem + d_col, sdesc_advance(ad, (kk >> 2) * KV_BOX + (kk & 3) * 32),
+                                sdesc_advance(bd, (kk >> 2) * Q_BOX + (kk & 3) * 32), idesc_ss, kk > 0);
                 };
-                int i = 0;
-                const int head = n_tot < 6 ? n_tot : 6;
-                for (; i < head; ++i) gen(i);                    // (i = 0 does not accumulate into dV / dK)
-                for (; i + 6 < n_tot; i += 6) {                  // i is a multiple of 6; the block's last iteration has a successor
-                    const uint32_t kp = (uint32_t)(i / 6) & 1u;
-                    step(std::integral_constant<int, 0>{}, kp); step(std::integral_constant<int, 1>{}, kp);
-                    step(std::integral_constant<int, 2>{}, kp); step(std::integral_constant<int, 3>{}, kp);
-                    step(std::integral_constant<int, 4>{}, kp); step(std::integral_constant<int, 5>{}, kp);
+                auto ts_step = [&](uint32_t a_col, uint64_t bd, uint32_t d_col, int kk, bool acc) {
+                    umma_f16_ts(tmem + d_col, tmem + a_col + (kk < 2 ? 8 * kk : 32 + 8 * (kk - 2)), sdesc_advance(bd, kk * 2048),
+                                idesc_ts, (acc || kk > 0) ? 1u : 0u);
+                };
+                constexpr int KS = DR / 16;                      // k-steps of M1 / M2 (8, or 4 for d = 64)
+                for (int i = 0; i < n_tot; ++i) {
+                    const int b = i & 1, s = i % NS, s1 = (i + 1) % NS;
+                    const bool nxt = i + 1 < n_tot;
+                    if (nxt) mbar_wait(&bar_in_full[s1], ((i + 1) / NS) & 1);
+                    mbar_wait(&bar_P[b], (i >> 1) & 1);
+                    tc_fence_after();
+                    B200_TRB(2, i, 1);
+                    {                                                                       // G1
+                        const uint64_t qd = make_sdesc(sb + OFF_Q + s1 * Q_TILE, 16, 1024, 2);
+                        const uint64_t dod = make_sdesc(sb + OFF_DO + s * Q_TILE, Q_BOX, 1024, 2);
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            if (nxt) {
+#pragma unroll
+                                for (int u = 0; u < KS / 4; ++u) ss_step(k_kmaj, qd, TM_S + 64 * (b ^ 1), (KS / 4) * t + u);
+                            }
+                            ts_step(TM_S + 64 * b, dod, TM_DV, t, i > 0);
+                        }
+                        if (nxt) umma_commit(&bar_S[b ^ 1]);
+                    }
+                    B200_TRB(2, i, 2);
+                    mbar_wait(bar_dS, i & 1);
+                    mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
+                    tc_fence_after();
+                    B200_TRB(2, i, 3);
+                    {                                                                       // G2
+                        const uint64_t dsd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
+                        const uint64_t qmn = make_sdesc(sb + OFF_Q + s * Q_TILE, Q_BOX, 1024, 2);
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(k_mnmaj, (2 * t) * 2048), sdesc_advance(dsd, (2 * t) * 2048), idesc_dq, t > 0);
+                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(k_mnmaj, (2 * t + 1) * 2048), sdesc_advance(dsd, (2 * t + 1) * 2048), idesc_dq, 1u);
+                            ts_step(TM_DP, qmn, TM_DK, t, i > 0);
+                        }
+                        umma_commit(&bar_in_empty[s]);
+                        umma_commit(bar_dQ_full);
+                    }
+                    B200_TRB(2, i, 4);
+                    if (nxt) {                                                              // G3
+                        const uint64_t dod1 = make_sdesc(sb + OFF_DO + s1 * Q_TILE, 16, 1024, 2);
+#pragma unroll
+                        for (int kk = 0; kk < KS; ++kk) ss_step(v_kmaj, dod1, TM_DP, kk);
+                        umma_commit(bar_dP);
+                    }
+                    B200_TRB(2, i, 6);
                 }
-                for (; i < n_tot; ++i) gen(i);
             } else {
                 for (int i = 0; i < n_tot; ++i) gen(i);
             }
@@ -485,7 +525,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         }
     } else if (warp >= 4 && warp < 12) {
         const int w = (warp - 4) >> 2;
-        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_tot, n_it, qt_min, i_off, kv0, causal, scale_log2, scale);
+        bwd_compute_role(w, tmem, smem, bar_in_full, bar_S, bar_dP, bar_P, bar_dS, n_tot, n_it, qt_min, i_off, kv0, causal, scale_log2, scale, dbg);
         mbar_wait(bar_done, 0);
         tc_fence_after();
         bwd_epilogue<DR>(w, tmem, smem, w == 0 ? &tmdV : &tmdK, kv0, hk, b);
@@ -603,9 +643,12 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
         make_tmap_4d(&tmdV, a.dV, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldv.sb, a.ldv.sh, a.ldv.sn, BN, 64))
         return B200_ERR_CUDA;
     dim3 grid((a.Nkv + BN - 1) / BN, a.Hkv, a.Bm);
-    // experiment hook, timing only (wrong dQ): B200_BWD_DBG bit 0 skips the dQ reduce-adds, bit 1 issues plain stores instead
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? (atoi(e) & 3) : 0; }
+#ifdef B200_EXPERIMENTS
+    static int dbg = -1;                     // timing-only hooks, side libraries only (see B200_DBG above)
+    if (dbg < 0) { const char* e = getenv("B200_BWD_DBG"); dbg = e ? atoi(e) : 0; }
+#else
+    const int dbg = 0;
+#endif
     bwd_kernel<DR, ISSUE><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
                                                 a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
                                                 a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
@@ -614,13 +657,27 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     return B200_OK;
 }
 
-// B200_BWD_VARIANT=1 selects the experimental issue loop (bwd_kernel<128, 1>); d = 64 always runs the measured one
-static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st)
+#ifdef B200_EXPERIMENTS
+// side libraries only: B200_BWD_VARIANT=2 selects the interleaved issue order (r2: correct, 8 % slower -- the kernel is
+// bound by shared-memory traffic, not by the order of its MMAs: profiles/r2a_bwd_interleaved_negative.txt)
+static int bwd_variant()
 {
     static int variant = -1;
     if (variant < 0) { const char* e = getenv("B200_BWD_VARIANT"); variant = e ? atoi(e) : 0; }
-    return variant == 1 ? bwd_launch<128, 1>(a, st) : bwd_launch<128>(a, st);
+    return variant;
 }
+static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st)
+{
+    return bwd_variant() == 2 ? bwd_launch<128, 2>(a, st) : bwd_launch<128>(a, st);
+}
+static int bwd_launch_d64(const BwdLaunch& a, cudaStream_t st)
+{
+    return bwd_variant() == 2 ? bwd_launch<64, 2>(a, st) : bwd_launch<64>(a, st);
+}
+#else
+static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st) { return bwd_launch<128>(a, st); }
+static int bwd_launch_d64(const BwdLaunch& a, cudaStream_t st) { return bwd_launch<64>(a, st); }
+#endif
 
 // contiguous [BH, N, 128 or 64] slabs (the reference layout); BH is cut into (batches x heads) that fit the grid limits
 static BwdLaunch contiguous_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
@@ -649,7 +706,7 @@ static int bwd_run(const BwdLaunch& a, int BHq, int d, void* ws, void* dQ, const
     B200_CUDA_TRY(cudaMemsetAsync(dQacc, 0, n_dq * sizeof(float), st));
     BwdLaunch b = a;
     b.L2p = L2p; b.Dp = Dp; b.dQacc = dQacc;
-    if (d == 128) B200_TRY(bwd_launch_d128(b, st)); else B200_TRY(bwd_launch<64>(b, st));
+    if (d == 128) B200_TRY(bwd_launch_d128(b, st)); else B200_TRY(bwd_launch_d64(b, st));
     if (ldq == nullptr) {
         unsigned cgrid = (unsigned)((n_dq / 4 + 255) / 256);
         if (cgrid > 148u * 8) cgrid = 148u * 8;

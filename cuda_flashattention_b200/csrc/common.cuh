@@ -76,7 +76,7 @@ int launch_fwd_split(const FwdArgs& a, int BH_valid, cudaStream_t st);   // expe
 bool fwd_pair_eligible(const FwdArgs& a);                                // experimental variant (fwd_pair_sm100.cu): CTA pairs,
 int launch_fwd_pair(const FwdArgs& a, int BH_valid, cudaStream_t st);    //   bf16 d = 128 non-causal, Nq % 512 == 0, Nkv % 128 == 0
 int launch_fwd_shs(const FwdArgs& a, int BH_valid, cudaStream_t st);     // experimental variant (fwd_shs_sm100.cu), bf16 d = 128
-int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st);    // experimental variant (fwd_dbuf_sm100.cu), bf16 d = 128
+int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st);    // the shipped bf16 d = 128 forward (fwd_dbuf_sm100.cu)
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,

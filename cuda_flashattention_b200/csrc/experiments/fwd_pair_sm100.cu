@@ -29,9 +29,9 @@
 // the shared-memory traffic buys nothing back.  Kept as a working reference for the cta_group::2 protocol (2-CTA TMA
 // completion on the leader's barriers, multicast commits, remote arrivals, pair-wide TMEM allocation, tear-down drain);
 // never selected by default.  tools/try_fwd_variant.sh 3 re-runs the measurement.
-#include "common.cuh"
-#include "ptx.cuh"
-#include "tmap.h"
+#include "../common.cuh"
+#include "../ptx.cuh"
+#include "../tmap.h"
 #include <stdlib.h>
 
 namespace b200 {

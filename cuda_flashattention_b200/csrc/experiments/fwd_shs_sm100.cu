@@ -25,9 +25,9 @@
 // makes the round trip  issue -> (queue behind the PV MMAs of the in-order tensor pipe) -> 512 clk -> commit -> tcgen05.ld
 // before the OTHER tile's score MMA may even be issued, twice per 128 keys; that round trip replaces the chain it
 // removed.  (ptxas also spills the 16 speculated P registers per step at the 216-register budget.)  Kept opt-in.
-#include "common.cuh"
-#include "ptx.cuh"
-#include "tmap.h"
+#include "../common.cuh"
+#include "../ptx.cuh"
+#include "../tmap.h"
 #include <stdlib.h>
 #include <type_traits>
 

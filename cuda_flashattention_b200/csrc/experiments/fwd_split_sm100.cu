@@ -15,9 +15,9 @@
 // RESULT (r1(c)): correct but 14 % SLOWER than fwd_sm100.cu at C3 (3.77 vs 3.29 ms) -- the N = 64 score
 // halves read the Q tile twice and are operand-fetch-bound, and the in-order issuing thread has three hand-offs per
 // tile step.  Kept for the record and for further experiments; never selected by default.
-#include "common.cuh"
-#include "ptx.cuh"
-#include "tmap.h"
+#include "../common.cuh"
+#include "../ptx.cuh"
+#include "../tmap.h"
 #include <stdlib.h>
 #include <type_traits>
 

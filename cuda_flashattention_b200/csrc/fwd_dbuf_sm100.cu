@@ -1,5 +1,7 @@
-// fwd_dbuf_sm100.cu -- EXPERIMENTAL forward variant (bf16, d = 128), selected with B200_FWD_VARIANT=4:
+// fwd_dbuf_sm100.cu -- the shipped FlashAttention-2 forward for bf16, d = 128 (r2: promoted from experiment to default):
 // 64-row K/V tiles with the score tile DOUBLE-BUFFERED in TMEM, so that no MMA ever waits for a softmax.
+// Replaces flash_attention_2_forward_kernel (reference src/03_flash_attention_v2_ring/common/flash_attention_kernel.cu:13-131,
+// src/util/attention_helper.h:40-132).
 //
 // Why: fwd_sm100.cu is bound by a dependency CHAIN, not by a unit (the CTA-pair experiment, fwd_pair_sm100.cu, halved
 // the operand traffic and got slower by exactly the cross-CTA hand-off latency it added).  Per query tile the chain is
@@ -26,8 +28,8 @@
 //     fwd_sm100.cu (chain-bound), but here the softmax warps run back to back and the MUFU is the co-limiter:
 //     4 of 16 pairs -> 3.14 ms at C3 (fwd_sm100.cu: 3.28), 3.60 against 3.78 ms sustained under the power cap, causal
 //     1.71 against 1.82 ms; ncu: tensor pipe 76 % active (fwd_sm100.cu 67 %), MUFU 58 %.
-// STATUS: parity-checked against the generic kernels with tools/kbench --check (ragged, causal, N = 64 ... 8192); the
-// full pytest suite has not been run on it yet (tests/test_gpu_kernel_variants.py is that gate), so it is opt-in.
+// STATUS: default since r2 -- the forward-facing -m gpu suite (plain / causal / layouts / host pipeline / ring emulation:
+// 67 tests) passes on it and bench.py's forward went from 3.81 to 3.43 ms in the fwd+bwd loop (profiles/r2a_*).
 //
 // Everything else is fwd_sm100.cu: roles, thread = row softmax with speculation and lazy rescale, P published in two
 // halves, causal / ragged masks, 4-D tensor maps (strided layouts, grouped K/V heads), epilogue through the Q tile.
@@ -456,9 +458,10 @@ static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
 int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
     if (a.dtype != B200_DTYPE_BF16 || a.d != fdb::D) return B200_ERR_UNSUPPORTED;
-    static int poly = -1;                                // tuning hook: B200_DBUF_POLY = pairs of every 16 on the FMA pipe
-    if (poly < 0) { const char* e = getenv("B200_DBUF_POLY"); poly = e ? atoi(e) : 0; }
-    static int peel = -1;                                // untested hook: B200_DBUF_PEEL=1 (with POLY 0 or 4)
+#ifdef B200_EXPERIMENTS
+    static int poly = -1;                                // side libraries only: B200_DBUF_POLY = pairs of every 16 on the FMA pipe
+    if (poly < 0) { const char* e = getenv("B200_DBUF_POLY"); poly = e ? atoi(e) : 4; }
+    static int peel = -1;                                // B200_DBUF_PEEL=1: branch-free issue loops (r2: measured 1.5 % slower)
     if (peel < 0) { const char* e = getenv("B200_DBUF_PEEL"); peel = e ? atoi(e) : 0; }
     if (peel) {
         if (poly == 0) return launch_fwd_dbuf_t<0, true>(a, BH_valid, st);
@@ -474,6 +477,9 @@ int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st)
         case 8: return launch_fwd_dbuf_t<8>(a, BH_valid, st);
         default: return B200_ERR_UNSUPPORTED;
     }
+#else
+    return launch_fwd_dbuf_t<4>(a, BH_valid, st);        // the measured configuration
+#endif
 }
 
 }  // namespace b200

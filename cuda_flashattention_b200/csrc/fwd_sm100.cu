@@ -524,27 +524,39 @@ bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
     return d == 64 || d == 128;
 }
 
+// Shipped configuration, selected on shape and dtype only:
+//   bf16 d = 128 : fwd_dbuf_kernel<4> (fwd_dbuf_sm100.cu: 64-key tiles, double-buffered scores, one issuing thread per
+//                  tile, 4 of 16 exp2 pairs on the FMA pipe) -- promoted in r2 after the full -m gpu suite, +5 % burst /
+//                  +11 % in the bench loop over this file's 128-key kernel (profiles/r2a_*);
+//   bf16 d = 64, fp32 (tf32 MMAs) d = 64 / 128 : fwd_kernel<FwdCfg<...>> of this file.
+// The measured-negative variants (split-S, CTA pairs, shared score buffer, two issuers on this kernel, POLY / SPLITP
+// sweeps) live in csrc/experiments/ and are only compiled into `make EXPERIMENTS=1` side libraries, where
+// B200_FWD_VARIANT selects them for A/B timing; the product library has no environment hooks.
 static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
     if (a.dtype == B200_DTYPE_BF16) {
-        static int variant = -1;                         // tuning hook: B200_FWD_VARIANT = 10 * POLY + SPLITP
-        if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 1; }
         if (a.d == 128) {
-            if (variant == 2) return launch_fwd_split(a, BH_valid, st);       // experimental: split-S pipeline
-            if (variant == 3) {                                               // experimental: CTA pairs (cta_group::2)
+#ifdef B200_EXPERIMENTS
+            static int variant = -1;
+            if (variant < 0) { const char* e = getenv("B200_FWD_VARIANT"); variant = e ? atoi(e) : 4; }
+            if (variant == 2) return launch_fwd_split(a, BH_valid, st);       // split-S pipeline
+            if (variant == 3) {                                               // CTA pairs (cta_group::2)
                 if (fwd_pair_eligible(a)) return launch_fwd_pair(a, BH_valid, st);
                 return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true>>(a, BH_valid, st);
             }
-            if (variant == 4) return launch_fwd_dbuf(a, BH_valid, st);        // experimental: 64-key tiles, double-buffered S
-            if (variant == 6) return launch_fwd_shs(a, BH_valid, st);         // experimental: one shared score buffer, P apart
-            if (variant == 5)                                                 // experimental: one MMA-issuing thread per tile
+            if (variant == 6) return launch_fwd_shs(a, BH_valid, st);         // one shared score buffer, P apart
+            if (variant == 5)                                                 // one MMA-issuing thread per tile
                 return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, 0, true, 2>>(a, BH_valid, st);
-            switch (variant) {
+            if (variant != 4) {
+                switch (variant) {                                            // 10 * POLY + SPLITP; 1 = the r1 default
 #define B200_V(P, S) case 10 * P + S: return launch_fwd<FwdCfg<__nv_bfloat16, 128, 2, 128, P, S != 0>>(a, BH_valid, st);
-                B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
+                    B200_V(0, 0) B200_V(0, 1) B200_V(4, 1) B200_V(6, 0) B200_V(6, 1) B200_V(8, 1) B200_V(10, 1)
 #undef B200_V
-                default: return B200_ERR_UNSUPPORTED;
+                    default: return B200_ERR_UNSUPPORTED;
+                }
             }
+#endif
+            return launch_fwd_dbuf(a, BH_valid, st);
         }
         return launch_fwd<FwdCfg<__nv_bfloat16, 64, 2, 128, 0, true>>(a, BH_valid, st);
     }

@@ -105,7 +105,11 @@ static bool load_memops()
     return true;
 }
 
-enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_COUNT = 16 };
+enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_CALL_DONE = 8, F_COUNT = 16 };
+
+// transport preference (b200_ring_set_transport): -1 = B200_RING_TRANSPORT decides (default: copy engines), 0 = copy engines,
+// 1 = NCCL send/recv.  Collective like the ring calls themselves: every rank holds the same value.
+static int g_transport_pref = -1;
 
 struct PeerLink {
     ncclComm_t comm = nullptr;
@@ -118,6 +122,8 @@ struct PeerLink {
     uint32_t* prev_flags = nullptr;
     void* opened[4] = {nullptr, nullptr, nullptr, nullptr};   // mappings to close
     size_t exported = 0;                    // scratch size the neighbours have mapped
+    void* exported_ptr = nullptr;           // ... and its address (an NCCL-transport call may have re-allocated it since)
+    uint32_t calls_done = 0;                // ring calls finished on this link (F_CALL_DONE handshake)
     uint32_t push_kv[2] = {0, 0}, in_kv[2] = {0, 0}, rel_kv[2] = {0, 0};
     uint32_t push_acc[2] = {0, 0}, in_acc[2] = {0, 0}, out_acc[2] = {0, 0};
 };
@@ -156,10 +162,12 @@ static int link_prepare(RingState* rs, ncclComm_t comm, int rank, int nranks, si
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     PeerLink& L = g_link[dev];
-    static int want_ce = -1;
-    if (want_ce < 0) { const char* e = getenv("B200_RING_TRANSPORT"); want_ce = (e && !strcmp(e, "nccl")) ? 0 : 1; }
+    static int env_ce = -1;
+    if (env_ce < 0) { const char* e = getenv("B200_RING_TRANSPORT"); env_ce = (e && !strcmp(e, "nccl")) ? 0 : 1; }
+    const int want_ce = g_transport_pref < 0 ? env_ce : (g_transport_pref == 0 ? 1 : 0);
     const bool new_comm = (L.comm != comm || L.rank != rank || L.nranks != nranks);
-    const bool grow = rs->bytes < need;
+    // (re-export also when a call on the NCCL transport re-allocated the scratch the neighbours still have mapped)
+    const bool grow = rs->bytes < need || (L.ok && (rs->buf != L.exported_ptr || rs->bytes != L.exported));
     if (!want_ce || nranks > 255) {
         B200_TRY(ring_scratch(rs, need, scratch));
         *use_ce = false;
@@ -212,7 +220,7 @@ static int link_prepare(RingState* rs, ncclComm_t comm, int rank, int nranks, si
     B200_TRY(link_allgather(L, rs, mine, all));
     for (int r = 0; r < nranks; ++r) ok = ok && all[r].ok;
     if (!ok) link_close(L);
-    L.ok = ok; L.exported = rs->bytes;
+    L.ok = ok; L.exported = rs->bytes; L.exported_ptr = rs->buf;
     *use_ce = ok;
     return B200_OK;
 }
@@ -228,6 +236,24 @@ static inline int write_val(cudaStream_t st, uint32_t* addr, uint32_t v)
     B200_CU_TRY(g_write32(st, (CUdeviceptr)(uintptr_t)addr, v, CU_STREAM_WRITE_VALUE_DEFAULT));
     return B200_OK;
 }
+// Cross-call handshake of the copy-engine transport.  The per-buffer counters only order the hand-offs INSIDE a call;
+// the scratch regions of consecutive calls alias (forward partials / backward accumulators / receive slots), and a
+// fast rank could push the first block of call n+1 into a neighbour that is still reading call n's results.  So every
+// call ends by telling the PREVIOUS rank "I have read everything call n left in my scratch" (call_end, ordered behind
+// the call's last kernel on the caller's stream), and begins by waiting for that message from the NEXT rank -- the
+// only rank it writes into -- before its first push (call_begin).
+static int call_begin(PeerLink& L, RingState* rs)
+{
+    if (L.calls_done > 0) B200_TRY(wait_ge(rs->comm_stream, L.flags + F_CALL_DONE, L.calls_done));
+    return B200_OK;
+}
+static int call_end(PeerLink& L, RingState* rs, cudaStream_t st)
+{
+    B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
+    B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+    return write_val(rs->comm_stream, L.prev_flags + F_CALL_DONE, ++L.calls_done);
+}
+
 // push two buffers into the next rank's K/V receive slot
 static int ce_push_kv(PeerLink& L, RingState* rs, int slot, const void* k, const void* v, size_t off_k, size_t off_v, size_t bytes)
 {
@@ -325,9 +351,11 @@ static int cast_out(void* out, const float* acc, size_t n, int dtype, cudaStream
 static int exchange(const void* const* send, void* const* recv, const size_t* bytes, int n, int next, int prev,
                     ncclComm_t comm, cudaStream_t st)
 {
-    static int dbg = -1;                 // experiment hook: B200_RING_DBG=1 skips the transfers (timing only, wrong results)
+#ifdef B200_EXPERIMENTS
+    static int dbg = -1;                 // side libraries only: B200_RING_DBG=1 skips the transfers (timing only, wrong results)
     if (dbg < 0) { const char* e = getenv("B200_RING_DBG"); dbg = e ? atoi(e) : 0; }
     if (dbg & 1) return B200_OK;
+#endif
     B200_NCCL_TRY(ncclGroupStart());
     for (int i = 0; i < n; ++i) {
         B200_NCCL_TRY(ncclSend(send[i], bytes[i], ncclInt8, next, comm, st));
@@ -348,6 +376,13 @@ int b200_ring_kv_block(int rank, int step, int nranks)
     if (nranks <= 0) return -1;
     int b = (rank - step) % nranks;
     return b < 0 ? b + nranks : b;
+}
+
+int b200_ring_set_transport(int mode)
+{
+    if (mode < -1 || mode > 1) return B200_ERR_INVALID_ARGUMENT;
+    g_transport_pref = mode;
+    return B200_OK;
 }
 
 int b200_ring_unique_id(void* out128)
@@ -460,6 +495,7 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     if (ce) {
         B200_CUDA_TRY(cudaStreamWaitEvent(rs->attn_stream[0], rs->ev_main, 0));
         B200_CUDA_TRY(cudaStreamWaitEvent(rs->attn_stream[1], rs->ev_main, 0));
+        B200_TRY(call_begin(lk, rs));
     }
 
     const void* Kc = K; const void* Vc = V;
@@ -542,6 +578,7 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
         // the caller may reuse K/V (the source of the first push) once its stream has passed this call
         B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
         B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
+        B200_TRY(call_end(lk, rs, st));           // (behind the final merge: the partials have been read)
     }
     return B200_OK;
 }
@@ -635,6 +672,7 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
     B200_CUDA_TRY(cudaMemsetAsync(dVa[0], 0, acc_bytes, st));
     B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
     B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+    if (ce) B200_TRY(call_begin(lk, rs));
 
     // Step s: block b = (rank - s) mod P is resident (K/V in Kc/Vc, its running fp32 dK/dV in acc[cur]).
     // Compute partial grads, add them, then pass (dK,dV) accumulators on; K/V for step s+1 are
@@ -723,6 +761,7 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
     B200_TRY(cast_out(dQ, dQa, n_el, dtype, st));
     B200_TRY(cast_out(dK, dKa[cur], n_el, dtype, st));
     B200_TRY(cast_out(dV, dVa[cur], n_el, dtype, st));
+    if (ce) B200_TRY(call_end(lk, rs, st));          // (behind the casts: the home accumulators have been read)
     return B200_OK;
 }
 

@@ -244,6 +244,18 @@ B200_API int b200_ring_comm_destroy(ncclComm_t comm);
 B200_API int b200_ring_exchange_kv(const void* send_k, void* recv_k, const void* send_v, void* recv_v, size_t bytes_each,
                           int next_rank, int prev_rank, ncclComm_t comm, cudaStream_t stream);
 
+/* Data plane of the ring calls (K/V blocks and, in the backward, the travelling dK/dV accumulators):
+ *   B200_RING_TRANSPORT_AUTO (-1, default) : copy-engine pushes over NVLink through CUDA-IPC mappings when every rank can
+ *       map its neighbours, else NCCL; the environment variable B200_RING_TRANSPORT=nccl selects NCCL;
+ *   B200_RING_TRANSPORT_COPY_ENGINE (0)    : as AUTO, ignoring the environment variable;
+ *   B200_RING_TRANSPORT_NCCL (1)           : grouped ncclSend/ncclRecv -- exactly what the reference's ring_exchange_kv
+ *       does (src/util/nccl_utils.h:133-142).
+ * Collective like the ring calls: every rank sets the same mode between the same two ring calls. */
+#define B200_RING_TRANSPORT_AUTO (-1)
+#define B200_RING_TRANSPORT_COPY_ENGINE 0
+#define B200_RING_TRANSPORT_NCCL 1
+B200_API int b200_ring_set_transport(int mode);
+
 /* Frees the library's per-device scratch arena (optional; also released at process exit). */
 B200_API int b200_release_workspace(void);
 

@@ -141,6 +141,34 @@ def backward(Q, K, V, dO, scale=0.0, causal=False):
     return dQ, dK, dV
 
 
+def row_stats(Q, K, V, dO, scale=0.0):
+    """Per query row: (log-sum-exp of the scaled scores, delta = sum_j P_ij dP_ij), fp64, all host threads."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
+    Nq, d = Q.shape; Nkv = K.shape[0]
+    lse = np.empty((Nq,), np.float64); delta = np.empty((Nq,), np.float64)
+    lib().oracle_row_stats(q, k, v, g, lse.ctypes.data_as(_dp), delta.ctypes.data_as(_dp),
+                           C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return lse, delta
+
+
+def backward_rows(Q, K, V, dO, qrows, kvrows, scale=0.0, stats=None):
+    """Row-sampled backward: dQ for the query rows `qrows`, (dK, dV) for the key rows `kvrows` -- the arithmetic of
+    oracle.backward (naive_attention_backward, src/util/naive_attention.h:84-161) on those rows only.  `stats` =
+    (lse, delta) for every query row; None computes them here (row_stats: O(Nq Nkv d))."""
+    Q, q = _f(Q); K, k = _f(K); V, v = _f(V); dO, g = _f(dO)
+    Nq, d = Q.shape; Nkv = K.shape[0]
+    lse, delta = row_stats(Q, K, V, dO, scale) if stats is None else stats
+    lse = np.ascontiguousarray(lse, dtype=np.float64); delta = np.ascontiguousarray(delta, dtype=np.float64)
+    assert lse.shape == (Nq,) and delta.shape == (Nq,)
+    qrows = np.ascontiguousarray(qrows, dtype=np.int32); kvrows = np.ascontiguousarray(kvrows, dtype=np.int32)
+    dQ = np.empty((len(qrows), d), np.float32); dK = np.empty((len(kvrows), d), np.float32); dV = np.empty((len(kvrows), d), np.float32)
+    lib().oracle_backward_rows(q, k, v, g, lse.ctypes.data_as(_dp), delta.ctypes.data_as(_dp),
+                               qrows.ctypes.data_as(_ip), C.c_int(len(qrows)), kvrows.ctypes.data_as(_ip), C.c_int(len(kvrows)),
+                               dQ.ctypes.data_as(_fp), dK.ctypes.data_as(_fp), dV.ctypes.data_as(_fp),
+                               C.c_int(Nq), C.c_int(Nkv), C.c_int(d), C.c_float(scale))
+    return dQ, dK, dV
+
+
 def ring_step(Q, Kblk, Vblk, O, Lbuf, M, scale, last_step):
     """In-place carry step, src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:67-139."""
     Q, q = _f(Q); Kblk, k = _f(Kblk); Vblk, v = _f(Vblk)
