@@ -191,9 +191,15 @@ def run_reference(args):
         times.append(s)
     per = sum(times) / len(times)
     val = 14.0 * heads * N * N * D0 / per / 1e12
+    cfg = config_dict(args.gpus)
+    # what this arm really times: a bounded sample (the naive backward is O(N^3), naive_attention.h:131-140) -- say so in
+    # `config` itself so that nobody pairs the two lines as like for like
+    cfg["sampled"] = {"B": 1, "H": heads, "N": N, "d": D0, "dtype": "f32",
+                      "note": f"reference CPU path on {heads} heads of N={N} (not N={cfg['N_total']}): its backward is O(N^3)"}
+    cfg["reference_sample_differs_from_gpu_config"] = True
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config_dict(args.gpus),
+            "dtype": "f32", "data": "synthetic", "config": cfg,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": heads, "kind": kind,
                              "sample": f"each step: {heads} heads x fwd+bwd at N={N} d={D0} fp32 on {heads} host threads"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -385,6 +391,44 @@ def run_ours(args):
         flops_rank = 14.0 * B * H * (Nt * (Nt + 1.0) / 2.0) / world * d
     value = world * flops_rank / (ms_per_step * 1e-3) / 1e12
 
+    # ---- N > 1: the two forward schedules side by side (outside the headline timed region; the headline ran the default)
+    ring_forward = None
+    if world > 1 and not CAUSAL:
+        def time_fwd(mode, n=5):
+            check(lib.b200_ring_set_forward_mode(mode), "set_forward_mode")
+            fwd(); fwd(); barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(n):
+                fwd()
+            a1.record()
+            barrier()
+            tt = torch.tensor([a0.elapsed_time(a1) / n], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+        ring_forward = {"stepwise_ms": time_fwd(1), "persistent_ms": time_fwd(2),
+                        "note": "one launch per ring step + n-way LSE merge vs ONE persistent launch waiting on arrival flags (SURVEY 8f-2); "
+                                "the headline line uses the library default (b200_ring_set_forward_mode(0))"}
+        check(lib.b200_ring_set_forward_mode(0), "set_forward_mode")
+        fwd(); bwd(); barrier()
+
+    # ---- parity gate on the outputs of the last timed step (outside every timed region)
+    parity = None
+    if not args.no_parity:
+        shape = (B, H, Nl, Nt, d)
+        tens = (q, k, v, dO, O, L, dQ, dK, dV)
+        parity = parity_check(torch, dist, fa, world, rank, CAUSAL, shape, tens)
+        if world > 1:
+            # the same check on the other data plane: NCCL send/recv (what the reference's ring_exchange_kv is)
+            parity = {"transport": {"copy_engine": parity}}
+            check(lib.b200_ring_set_transport(1), "set_transport")
+            fwd(); bwd(); barrier()
+            parity["transport"]["nccl"] = parity_check(torch, dist, fa, world, rank, CAUSAL, shape, tens, seed=1)
+            check(lib.b200_ring_set_transport(-1), "set_transport")
+            fwd(); bwd(); barrier()                      # back on the default transport for the e2e leg
+            if rank == 0:
+                parity["ok"] = bool(all(p_["ok"] for p_ in parity["transport"].values()))
+
     # ---- end to end: host (pinned) buffers in, host buffers out, copies inside the timed region
     hin = [torch.empty_like(x, device="cpu").pin_memory().copy_(x) for x in (q, k, v, dO)]
     hout2 = [[torch.empty_like(x, device="cpu").pin_memory() for x in (O, dQ, dK, dV)] for _ in range(2)]
@@ -393,43 +437,49 @@ def run_ours(args):
     side = [torch.cuda.Stream(), torch.cuda.Stream()]
 
     def e2e_step(i=0):
+        # the public host-buffer calls: pinned host tensors in, pinned host tensors out; chunks of (b,h) slabs are
+        # copied in, attended (fwd + bwd; at N > 1 a ring fwd + bwd per chunk) and copied out on three overlapping
+        # streams inside the library.  Consecutive steps are independent requests.
+        ho, hl = hout2[i & 1], hL2[i & 1]
         if world == 1:
-            # the public host-buffer call: pinned host tensors in, pinned host tensors out; chunks of (b,h) slabs
-            # are copied in, attended (fwd + bwd) and copied out on three overlapping streams inside the library.
-            # Consecutive steps are independent requests, issued on two alternating streams so the tail of one
-            # step's copy-out overlaps the head of the next step's copy-in (every step still moves all its bytes).
-            ho, hl = hout2[i & 1], hL2[i & 1]
+            # ... issued on two alternating streams so the tail of one step's copy-out overlaps the head of the next
+            # step's copy-in (every step still moves all its bytes)
             check(lib.b200_fa2_fwd_bwd_host(P(hin[0]), P(hin[1]), P(hin[2]), P(hin[3]), P(ho[0]), P(hl), P(ho[1]), P(ho[2]),
                                             P(ho[3]), B, H, Nl, d, 0.0, 0, side[i & 1].cuda_stream), "fwd_bwd_host")
-            return
-        for dst, src in zip((q, k, v, dO), hin):
-            dst.copy_(src, non_blocking=True)
-        fwd(); bwd()
-        for dst, src in zip(hout, (O, dQ, dK, dV)):
-            dst.copy_(src, non_blocking=True)
-        hL.copy_(L, non_blocking=True)
+        else:
+            # (ring calls are collective and share one scratch: one stream, step after step)
+            check(lib.b200_ring_fwd_bwd_host(P(hin[0]), P(hin[1]), P(hin[2]), P(hin[3]), P(ho[0]), P(hl), P(ho[1]), P(ho[2]),
+                                             P(ho[3]), B, H, Nl, d, 0.0, 0, FL, ch, rank, world, side[0].cuda_stream), "ring_fwd_bwd_host")
+
+    def timed_e2e(n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        cur = torch.cuda.current_stream()
+        e0.record()
+        for s_ in side:
+            s_.wait_stream(cur)
+        for i in range(n):
+            e2e_step(i)
+        for s_ in side:
+            cur.wait_stream(s_)
+        e1.record()
+        barrier()
+        t2 = torch.tensor([e0.elapsed_time(e1) / n], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        return float(t2.item())
 
     e2e_step()
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2e_single_ms = timed_e2e(1)                   # one call, nothing to overlap with but its own chunks
     n_e2e = max(1, min(args.steps, 8))
-    cur = torch.cuda.current_stream()
-    e0.record()
-    for s_ in side:
-        s_.wait_stream(cur)
-    for i in range(n_e2e):
-        e2e_step(i)
-    for s_ in side:
-        cur.wait_stream(s_)
-    e1.record()
-    barrier()
-    t2 = torch.tensor([e0.elapsed_time(e1) / n_e2e], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t2.item())
+    e2e_ms = timed_e2e(n_e2e)                      # a stream of calls (at N = 1 consecutive calls overlap on two streams)
+    e2e_kind = (f"throughput over {n_e2e} back-to-back host-buffer calls" +
+                (" on two alternating streams (copy-out of one overlaps copy-in of the next)" if world == 1 else "") +
+                "; single_call_ms is one call alone")
     h2d = sum(x.numel() * x.element_size() for x in hin)
     d2h = sum(x.numel() * x.element_size() for x in hout) + hL.numel() * 4
 
+    failed = False
     if rank == 0:
         pk = peaks()
         tc_bwd = bool(lib.b200_bwd_uses_tensor_cores(0, d, Nl, Nl))
@@ -447,10 +497,12 @@ def run_ours(args):
                     "kernel_family": "tcgen05" if tc_bwd else "generic CUDA-core (tcgen05 backward not built yet)"},
             "pct_of_nominal_2250": 100.0 * value / world / 2250.0,
             "roofline": {"bound": "tensor", "kernel": f"{dom} ({'whole ring pass incl. merge/accumulate kernels' if world > 1 else 'call incl. its small helper kernels'})",
-                         "achieved": achieved, "peak": pk["sustained"], "peak_src": f"{pk['src']} sustained bf16 (timed inside the step loop)",
-                         "unit": "TFLOP/s", "frac": achieved / pk["sustained"], "traffic": None},
+                         "achieved": achieved, "peak": pk["burst"],
+                         "peak_src": f"{pk['src']} bf16 dense: burst (cuBLAS 8192^3 best of 10); the sustained figure (4 s back to back, power-capped) is {pk['sustained']}",
+                         "unit": "TFLOP/s", "frac": achieved / pk["burst"], "frac_burst": achieved / pk["burst"],
+                         "frac_sustained": achieved / pk["sustained"], "traffic": None},
             "e2e": {"value": world * flops_rank / (e2e_ms * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": e2e_ms,
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "kind": e2e_kind, "single_call_ms": e2e_single_ms},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1:
@@ -459,12 +511,20 @@ def run_ours(args):
                 line["roofline"]["traffic"] = tr["bytes"]
                 line["roofline"]["traffic_note"] = (f"DRAM read+write bytes of one {dom}_kernel launch at this workload, ncu --set full, {tr['src']}; "
                                                     f"algorithmic bytes {'2.15e9' if dom == 'bwd' else '1.07e9'}")
+        if ring_forward is not None:
+            line["ring_forward"] = ring_forward
+        if parity is not None:
+            line["parity"] = parity
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line))
+        if parity is not None and not parity["ok"]:
+            failed = True
     if world > 1:
         comm.close()
         dist.destroy_process_group()
+    if failed:
+        raise SystemExit("parity check FAILED (see the 'parity' object of the JSON line)")
 
 
 def main():
@@ -477,6 +537,7 @@ def main():
                     help="c5 = the long-context ring config (not the driver's headline line)")
     ap.add_argument("--causal", action="store_true", help="causal extension (not the driver's headline line)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle parity gate (profiling runs)")
     args = ap.parse_args()
     globals()["WORKLOAD"] = args.workload
     globals()["CAUSAL"] = args.causal

@@ -11,7 +11,9 @@ import os
 import torch  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200attn.so")
+# B200ATTN_LIB: development override (tools/kbench reads the same variable) to load a side build -- libb200attn_exp.so,
+# the product plus the experimental kernel variants, or libb200attn_trace.so -- instead of the product library.
+LIB_PATH = os.environ.get("B200ATTN_LIB") or os.path.join(_HERE, "libb200attn.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -47,6 +49,8 @@ _SIGS = {
     "b200_debug_launch_count": (C.c_ulonglong, []),
     "b200_fwd_uses_tensor_cores": (_i, [_i, _i, _i, _i]),
     "b200_bwd_uses_tensor_cores": (_i, [_i, _i, _i, _i]),
+    "b200_fa2_fwd_route": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _i]),
+    "b200_fa2_bwd_route": (_i, [_vp] * 7 + [_i, _i, _i, _f, _i, _i]),
     "b200_fa2_fwd_f32": (_i, [_vp, _vp, _vp, _vp, _fp, _i, _i, _f, _vp]),
     "b200_fa2_bwd_f32": (_i, [_vp] * 9 + [_i, _i, _f, _vp]),
     "b200_fa1_fwd_f32": (_i, [_vp] * 6 + [_i, _i, _vp]),
@@ -70,6 +74,8 @@ _SIGS = {
     "b200_ring_zigzag_chunk": (_i, [_i, _i, _i]),
     "b200_ring_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
     "b200_ring_set_transport": (_i, [_i]),
+    "b200_ring_set_forward_mode": (_i, [_i]),
+    "b200_ring_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
     "b200_ring_unique_id": (_i, [_vp]),
     "b200_ring_comm_init": (_i, [C.POINTER(C.c_void_p), _vp, _i, _i]),
     "b200_ring_comm_destroy": (_i, [_vp]),

@@ -160,17 +160,31 @@ def flash_attention_2_forward_backward_host(Q, K, V, dO, softmax_scale=0.0, out=
 # grouped K/V heads (GQA / MQA) and an autograd function, all through b200_fa2_fwd_desc / _bwd_desc.
 # The reference stops at contiguous single-head slabs (__info__/README.md:175).
 # ---------------------------------------------------------------------------------------------------
+def _dense(t):
+    """A view the descriptors can express: last dimension contiguous and no zero stride on a dimension of extent > 1
+    (autograd hands out expanded gradients, e.g. O.sum().backward(); the all-zero layout means "contiguous")."""
+    if t.stride(-1) != 1 or any(st == 0 and sz > 1 for st, sz in zip(t.stride(), t.shape)):
+        return t.contiguous()
+    return t
+
+
 def _dims(t, layout):
     """(B, H, N, d, Layout) of a 4-D tensor whose last dimension is contiguous."""
     if t.dim() != 4 or t.stride(-1) != 1:
         raise ValueError("expected a 4-D tensor with a contiguous last dimension")
     if layout == "bhnd":
         B, H, N, d = t.shape
-        return B, H, N, d, Layout(t.stride(0), t.stride(1), t.stride(2))
-    if layout == "bnhd":
+        sb, sh, sn = t.stride(0), t.stride(1), t.stride(2)
+    elif layout == "bnhd":
         B, N, H, d = t.shape
-        return B, H, N, d, Layout(t.stride(0), t.stride(2), t.stride(1))
-    raise ValueError("layout must be 'bhnd' or 'bnhd'")
+        sb, sh, sn = t.stride(0), t.stride(2), t.stride(1)
+    else:
+        raise ValueError("layout must be 'bhnd' or 'bnhd'")
+    # a dimension of extent 1 is never stepped over: give it a harmless non-zero stride
+    sn = sn if N > 1 else d
+    sh = sh if H > 1 else N * sn
+    sb = sb if B > 1 else max(H * sh, N * sn)
+    return B, H, N, d, Layout(sb, sh, sn)
 
 
 def _make_desc(q, k, v, layout, causal, softmax_scale):
@@ -191,6 +205,7 @@ def _make_desc(q, k, v, layout, causal, softmax_scale):
 
 def attention_forward(q, k, v, causal=False, softmax_scale=None, layout="bhnd"):
     """O (same dimension order as q, contiguous) and L [B,H,Nq] for strided / grouped-head inputs."""
+    q, k, v = _dense(q), _dense(k), _dense(v)
     desc, (B, H, Nq) = _make_desc(q, k, v, layout, causal, softmax_scale)
     O = torch.empty(q.shape, dtype=q.dtype, device=q.device)
     L = torch.empty(B, H, Nq, dtype=torch.float32, device=q.device)
@@ -202,9 +217,9 @@ def attention_forward(q, k, v, causal=False, softmax_scale=None, layout="bhnd"):
 
 
 def attention_backward(q, k, v, O, L, dO, causal=False, softmax_scale=None, layout="bhnd"):
+    q, k, v = _dense(q), _dense(k), _dense(v)
     desc, _ = _make_desc(q, k, v, layout, causal, softmax_scale)
-    if dO.stride(-1) != 1:
-        dO = dO.contiguous()
+    dO, O = _dense(dO), _dense(O)
     dQ = torch.empty(q.shape, dtype=q.dtype, device=q.device)
     dK = torch.empty(k.shape, dtype=k.dtype, device=k.device)
     dV = torch.empty(v.shape, dtype=v.dtype, device=v.device)
@@ -282,8 +297,7 @@ def attention_varlen_backward(q, k, v, O, L, dO, cu_seqlens_q, cu_seqlens_k, cau
     desc, lay = _packed_desc(q, k, v, causal, softmax_scale)
     cq, vq = _cu_array(cu_seqlens_q)
     ck, vk = _cu_array(cu_seqlens_k)
-    if dO.stride(-1) != 1:
-        dO = dO.contiguous()
+    dO, O = _dense(dO), _dense(O)
     dQ = torch.empty(q.shape, dtype=q.dtype, device=q.device)
     dK = torch.empty(k.shape, dtype=k.dtype, device=k.device)
     dV = torch.empty(v.shape, dtype=v.dtype, device=v.device)

@@ -63,6 +63,22 @@ static int g_force_generic = 0;   // test hook: route everything to the CUDA-cor
 static inline bool valid_dtype(int dt) { return dt == B200_DTYPE_BF16 || dt == B200_DTYPE_F32; }
 static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sqrtf((float)d) : s; }
 
+// The routing predicates, shared by the calls and by b200_fa2_fwd_route / b200_fa2_bwd_route so that what a caller is
+// told is what runs.  Tensor-core path: supported (dtype, d), causal only on square problems, 16-byte aligned bases
+// (TMA), scale > 0 (the kernels fold scale into the running max).  Everything else: generic CUDA-core kernels.
+static bool fwd_routes_tc(const void* Q, const void* K, const void* V, const void* O, int dtype, int d, int Nq, int Nkv,
+                          float scale, bool causal)
+{
+    const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
+    return !g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv) && (al & 15) == 0 && scale > 0.0f;
+}
+static bool bwd_routes_tc(const void* Q, const void* K, const void* V, const void* dO, const void* dQ, const void* dK,
+                          const void* dV, int dtype, int d, int Nq, int Nkv, bool causal)
+{
+    const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
+    return !g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv) && (al & 15) == 0;
+}
+
 static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
                     float scale, int dtype, cudaStream_t st, int flags = 0)
 {
@@ -75,7 +91,7 @@ static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float*
     B200_TRY(device_check());
     scale = resolve_scale(scale, d);
     // tensor-core causal path: square problems (the usual self-attention case); everything else runs on the generic kernels
-    if (!g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv))
+    if (fwd_routes_tc(Q, K, V, O, dtype, d, Nq, Nkv, scale, causal))
         return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st, causal);
     return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
 }
@@ -105,7 +121,7 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     float* D = reinterpret_cast<float*>(ws);
     const size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
     B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
-    if (!g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv))
+    if (bwd_routes_tc(Q, K, V, dO, dQ, dK, dV, dtype, d, Nq, Nkv, causal))
         return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
                       reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st, causal);
     return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
@@ -123,9 +139,12 @@ struct HostPipe {
 static HostPipe g_pipe[64];
 static std::mutex g_pipe_mu;
 
+// `compute(din, dout, dL, nh, stream)` enqueues the attention of one chunk of nh (b,h) slabs on `stream`;
+// min_chunks > 1 asks for at least that many chunks (ring: few slabs per rank, but they must still pipeline)
+template <class Compute>
 static int host_pipeline(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
-                         void* hdQ, void* hdK, void* hdV, bool do_bwd, int B, int H, int N, int d, float scale,
-                         int dtype, cudaStream_t st)
+                         void* hdQ, void* hdK, void* hdV, bool do_bwd, int B, int H, int N, int d,
+                         int dtype, cudaStream_t st, int min_chunks, Compute&& compute)
 {
     if (!valid_dtype(dtype) || B < 0 || H < 0 || N < 0 || d <= 0 || (long long)B * H > 0x7fffffffLL) return B200_ERR_INVALID_ARGUMENT;
     const int BH = B * H;
@@ -155,6 +174,7 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
     static size_t chunk_bytes = 0;                 // tuning hook: B200_HOST_CHUNK_MB
     if (!chunk_bytes) { const char* e = getenv("B200_HOST_CHUNK_MB"); chunk_bytes = (size_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20; }
     int hc = (int)(chunk_bytes / slab);
+    if (min_chunks > 1 && hc > (BH + min_chunks - 1) / min_chunks) hc = (BH + min_chunks - 1) / min_chunks;
     if (hc < 1) hc = 1;
     if (hc > BH) hc = BH;
     const int nchunks = (BH + hc - 1) / hc;
@@ -187,10 +207,7 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
         // attention (the output set b is free once chunk c-2 has been copied out)
         B200_CUDA_TRY(cudaStreamWaitEvent(P.comp, P.ev_in[b], 0));
         B200_CUDA_TRY(cudaStreamWaitEvent(P.comp, P.ev_out[b], 0));
-        B200_TRY(fwd_impl(din[0], din[1], din[2], dout[0], dL, nh, N, N, d, scale, dtype, P.comp));
-        if (do_bwd)
-            B200_TRY(bwd_impl(din[0], din[1], din[2], dout[0], dL, din[3], dout[1], dout[2], dout[3], nh, N, N, d, scale, dtype,
-                              nullptr, 0, P.comp));
+        B200_TRY(compute(din, dout, dL, nh, P.comp));
         B200_CUDA_TRY(cudaEventRecord(P.ev_done[b], P.comp));
         // device -> host
         B200_CUDA_TRY(cudaStreamWaitEvent(P.d2h, P.ev_done[b], 0));
@@ -244,6 +261,24 @@ int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generi
 int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
 int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_bwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
 
+int b200_fa2_fwd_route(const void* Q, const void* K, const void* V, const void* O, int Nq, int Nkv, int d, float scale,
+                       int dtype, int flags)
+{
+    if (!valid_dtype(dtype) || Nq < 1 || Nkv < 1 || d <= 0 || (flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
+    if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
+    return fwd_routes_tc(Q, K, V, O, dtype, d, Nq, Nkv, resolve_scale(scale, d), causal) ? B200_ROUTE_TENSOR_CORE : B200_ROUTE_GENERIC;
+}
+int b200_fa2_bwd_route(const void* Q, const void* K, const void* V, const void* dO, const void* dQ, const void* dK,
+                       const void* dV, int Nq, int Nkv, int d, float scale, int dtype, int flags)
+{
+    (void)scale;
+    if (!valid_dtype(dtype) || Nq < 1 || Nkv < 1 || d <= 0 || (flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
+    if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
+    return bwd_routes_tc(Q, K, V, dO, dQ, dK, dV, dtype, d, Nq, Nkv, causal) ? B200_ROUTE_TENSOR_CORE : B200_ROUTE_GENERIC;
+}
+
 int b200_fa2_fwd_f32(const float* Q, const float* K, const float* V, float* O, float* L, int N, int d, float scale, cudaStream_t st)
 { return fwd_impl(Q, K, V, O, L, 1, N, N, d, scale, B200_DTYPE_F32, st); }
 
@@ -272,11 +307,37 @@ int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, float* L,
 
 int b200_fa2_fwd_host(const void* hQ, const void* hK, const void* hV, void* hO, float* hL,
                       int B, int H, int N, int d, float scale, int dtype, cudaStream_t st)
-{ return host_pipeline(hQ, hK, hV, nullptr, hO, hL, nullptr, nullptr, nullptr, false, B, H, N, d, scale, dtype, st); }
+{
+    return host_pipeline(hQ, hK, hV, nullptr, hO, hL, nullptr, nullptr, nullptr, false, B, H, N, d, dtype, st, 1,
+                         [&](uint8_t** din, uint8_t** dout, float* dL, int nh, cudaStream_t cs) {
+                             return fwd_impl(din[0], din[1], din[2], dout[0], dL, nh, N, N, d, scale, dtype, cs);
+                         });
+}
 
 int b200_fa2_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
                           void* hdQ, void* hdK, void* hdV, int B, int H, int N, int d, float scale, int dtype, cudaStream_t st)
-{ return host_pipeline(hQ, hK, hV, hdO, hO, hL, hdQ, hdK, hdV, true, B, H, N, d, scale, dtype, st); }
+{
+    return host_pipeline(hQ, hK, hV, hdO, hO, hL, hdQ, hdK, hdV, true, B, H, N, d, dtype, st, 1,
+                         [&](uint8_t** din, uint8_t** dout, float* dL, int nh, cudaStream_t cs) {
+                             B200_TRY(fwd_impl(din[0], din[1], din[2], dout[0], dL, nh, N, N, d, scale, dtype, cs));
+                             return bwd_impl(din[0], din[1], din[2], dout[0], dL, din[3], dout[1], dout[2], dout[3], nh, N, N, d,
+                                             scale, dtype, nullptr, 0, cs);
+                         });
+}
+
+int b200_ring_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO, void* hO, float* hL,
+                           void* hdQ, void* hdK, void* hdV, int B, int H, int N_local, int d, float scale, int dtype, int flags,
+                           ncclComm_t comm, int rank, int nranks, cudaStream_t st)
+{
+    // every chunk is one ring forward + backward over its heads (collective: all ranks cut B*H the same way)
+    return host_pipeline(hQ, hK, hV, hdO, hO, hL, hdQ, hdK, hdV, true, B, H, N_local, d, dtype, st, 2,
+                         [&](uint8_t** din, uint8_t** dout, float* dL, int nh, cudaStream_t cs) {
+                             B200_TRY(b200_ring_fwd_ex(din[0], din[1], din[2], dout[0], dL, 1, nh, N_local, d, scale, dtype, flags,
+                                                       comm, rank, nranks, cs));
+                             return b200_ring_bwd_ex(din[0], din[1], din[2], dout[0], dL, din[3], dout[1], dout[2], dout[3], 1, nh,
+                                                     N_local, d, scale, dtype, flags, comm, rank, nranks, cs);
+                         });
+}
 
 int b200_fa2_fwd_ex(const void* Q, const void* K, const void* V, void* O, float* L, int B, int H, int Nq, int Nkv, int d,
                     float scale, int dtype, int flags, cudaStream_t st)

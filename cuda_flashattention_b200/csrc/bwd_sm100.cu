@@ -197,6 +197,7 @@ __device__ __forceinline__ void bwd_drain_role(uint32_t tmem, uint64_t* bar_dQ_f
 {
     using namespace bwd;
     (void)dbg;
+    (void)dbg;
     const int r = threadIdx.x & 127;                                   // d index == TMEM lane
     const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
     const bool lane0 = (threadIdx.x & 31) == 0;
@@ -298,10 +299,16 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 // DR = real head dimension (128 or 64).  The tile layout is the d = 128 one; for d = 64 only the first 64-wide box of
 // every tile is loaded and the MMAs run over 64 (M1, M2: K extent; M3, M4: N extent).  M5 has d as its M extent, which
 // stays 128: the second box of K is zero-filled once, so lanes 64..127 of dQ^T are zero and are not drained.
-// ISSUE selects the MMA thread's issue order: 0 = one MMA group after the other, 2 = SS / TS interleaved (see the loop).
-// (r2: an unrolled-by-six issue loop with merged waits, "ISSUE = 1", measured 4-5 % SLOWER at C3 and was removed:
-// profiles/r2a_bwd_variant1_negative.txt.)
-template <int DR, int ISSUE = 0>
+// r2 experiments on this kernel, all measured at C3 and all removed from the source again (DESIGN.md 4.2 has the reading):
+//   * issue loop unrolled by six with merged waits: -4 %              (profiles/r2a_bwd_variant1_negative.txt)
+//   * SS / TS MMAs interleaved as SS SS TS triples: correct, -8 %      (profiles/r2a_bwd_interleaved_negative.txt)
+//   * K^T resident in TMEM (M5 as a TS MMA) with S single-buffered: correct, level (the S -> P -> M3 -> M1 chain, ~2300 clk,
+//     replaces the pipe limit)
+//   * mbarrier.try_wait suspend hints: no effect                       (profiles/r2a_try_suspend_no_effect.txt)
+// The subtraction profile (profiles/r2a_bwd_subtraction_profile.txt) and tools/mma_rate.cu explain why: an SS MMA with
+// M = 128 costs >= 64 clk whatever N <= 128 is (the A tile is read from shared memory at 64 B/clk), so the three N = 64
+// SS groups cost 3 x 8 x 64 = 1536 clk and the two TS groups 512: 2048 clk per iteration against the measured ~2090.
+template <int DR>
 __global__ void __launch_bounds__(bwd::THREADS, 1)
 bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
            const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -452,75 +459,7 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
                 umma_commit(bar_dQ_full);
                 B200_TRB(2, i, 6);
             };
-            if constexpr (ISSUE == 2) {
-                // Interleaved issue order.  A lone run of N = 64 SS MMAs is operand-fetch-bound (6 KB of shared memory per
-                // 32 clk of math; tools/mma_rate.cu: ~46-63 clk each), a TS MMA with N = 128 is not (4 KB per 64 clk), and
-                // the fetch of an SS MMA overlaps the math of the TS MMA ahead of it (the probe's alternating case).  So
-                // the 24 SS and 8 TS MMAs of an iteration are issued as SS SS TS triples wherever the TMEM hazards allow:
-                //   G1 = M1(i+1) x M3(i)   (S[(i+1)&1] written, P^T in S[i&1] read: different buffers)
-                //   G2 = M5(i)   x M4(i)   (dQ columns written, dS^T in the dP columns read)
-                //   G3 = M2(i+1)           (overwrites the dP columns M4(i) reads: has to follow it)
-                // which also leaves two barrier waits per iteration instead of four.
-                const uint64_t k_kmaj = make_sdesc(sb + OFF_K, 16, 1024, 2), v_kmaj = make_sdesc(sb + OFF_V, 16, 1024, 2);
-                const uint64_t k_mnmaj = make_sdesc(sb + OFF_K, KV_BOX, 1024, 2);
-                auto ss_step = [&](uint64_t ad, uint64_t bd, uint32_t d_col, int kk) {
-                    umma_f16_ss(tmem + d_col, sdesc_advance(ad, (kk >> 2) * KV_BOX + (kk & 3) * 32),
-                                sdesc_advance(bd, (kk >> 2) * Q_BOX + (kk & 3) * 32), idesc_ss, kk > 0);
-                };
-                auto ts_step = [&](uint32_t a_col, uint64_t bd, uint32_t d_col, int kk, bool acc) {
-                    umma_f16_ts(tmem + d_col, tmem + a_col + (kk < 2 ? 8 * kk : 32 + 8 * (kk - 2)), sdesc_advance(bd, kk * 2048),
-                                idesc_ts, (acc || kk > 0) ? 1u : 0u);
-                };
-                constexpr int KS = DR / 16;                      // k-steps of M1 / M2 (8, or 4 for d = 64)
-                for (int i = 0; i < n_tot; ++i) {
-                    const int b = i & 1, s = i % NS, s1 = (i + 1) % NS;
-                    const bool nxt = i + 1 < n_tot;
-                    if (nxt) mbar_wait(&bar_in_full[s1], ((i + 1) / NS) & 1);
-                    mbar_wait(&bar_P[b], (i >> 1) & 1);
-                    tc_fence_after();
-                    B200_TRB(2, i, 1);
-                    {                                                                       // G1
-                        const uint64_t qd = make_sdesc(sb + OFF_Q + s1 * Q_TILE, 16, 1024, 2);
-                        const uint64_t dod = make_sdesc(sb + OFF_DO + s * Q_TILE, Q_BOX, 1024, 2);
-#pragma unroll
-                        for (int t = 0; t < 4; ++t) {
-                            if (nxt) {
-#pragma unroll
-                                for (int u = 0; u < KS / 4; ++u) ss_step(k_kmaj, qd, TM_S + 64 * (b ^ 1), (KS / 4) * t + u);
-                            }
-                            ts_step(TM_S + 64 * b, dod, TM_DV, t, i > 0);
-                        }
-                        if (nxt) umma_commit(&bar_S[b ^ 1]);
-                    }
-                    B200_TRB(2, i, 2);
-                    mbar_wait(bar_dS, i & 1);
-                    mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
-                    tc_fence_after();
-                    B200_TRB(2, i, 3);
-                    {                                                                       // G2
-                        const uint64_t dsd = make_sdesc(sb + OFF_DS + b * DS_TILE, 16, 1024, 2);
-                        const uint64_t qmn = make_sdesc(sb + OFF_Q + s * Q_TILE, Q_BOX, 1024, 2);
-#pragma unroll
-                        for (int t = 0; t < 4; ++t) {
-                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(k_mnmaj, (2 * t) * 2048), sdesc_advance(dsd, (2 * t) * 2048), idesc_dq, t > 0);
-                            umma_f16_ss(tmem + TM_DQ, sdesc_advance(k_mnmaj, (2 * t + 1) * 2048), sdesc_advance(dsd, (2 * t + 1) * 2048), idesc_dq, 1u);
-                            ts_step(TM_DP, qmn, TM_DK, t, i > 0);
-                        }
-                        umma_commit(&bar_in_empty[s]);
-                        umma_commit(bar_dQ_full);
-                    }
-                    B200_TRB(2, i, 4);
-                    if (nxt) {                                                              // G3
-                        const uint64_t dod1 = make_sdesc(sb + OFF_DO + s1 * Q_TILE, 16, 1024, 2);
-#pragma unroll
-                        for (int kk = 0; kk < KS; ++kk) ss_step(v_kmaj, dod1, TM_DP, kk);
-                        umma_commit(bar_dP);
-                    }
-                    B200_TRB(2, i, 6);
-                }
-            } else {
-                for (int i = 0; i < n_tot; ++i) gen(i);
-            }
+            for (int i = 0; i < n_tot; ++i) gen(i);
             umma_commit(bar_done);
         }
     } else if (warp >= 4 && warp < 12) {
@@ -620,7 +559,7 @@ struct BwdLaunch {
     int stat_stride = 0, dq_rows = 0;    // floats per slab of L2p / Dp and rows per slab of dQacc; 0 = pad64(Nq) / Nq
 };
 
-template <int DR, int ISSUE = 0>
+template <int DR>
 static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 {
     using namespace bwd;
@@ -629,19 +568,20 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR, ISSUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(bwd_kernel<DR>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int Nq_pad = (a.Nq + 63) / 64 * 64, Hq = a.Hkv * a.G;
     CUtensorMap tmQ, tmK, tmV, tmdO, tmdK, tmdV;
     const CUtensorMapDataType bf = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-    if (make_tmap_4d(&tmQ, a.Q, bf, 2, a.Bm, Hq, a.Nq, DR, a.lq.sb, a.lq.sh, a.lq.sn, BM, 64) ||
-        make_tmap_4d(&tmdO, a.dO, bf, 2, a.Bm, Hq, a.Nq, DR, a.ldo.sb, a.ldo.sh, a.ldo.sn, BM, 64) ||
-        make_tmap_4d(&tmK, a.K, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lk.sb, a.lk.sh, a.lk.sn, BN, 64) ||
-        make_tmap_4d(&tmV, a.V, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lv.sb, a.lv.sh, a.lv.sn, BN, 64) ||
-        make_tmap_4d(&tmdK, a.dK, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldk.sb, a.ldk.sh, a.ldk.sn, BN, 64) ||
-        make_tmap_4d(&tmdV, a.dV, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldv.sb, a.ldv.sh, a.ldv.sn, BN, 64))
-        return B200_ERR_CUDA;
+    int trc = 0;
+    if ((trc = make_tmap_4d(&tmQ, a.Q, bf, 2, a.Bm, Hq, a.Nq, DR, a.lq.sb, a.lq.sh, a.lq.sn, BM, 64)) ||
+        (trc = make_tmap_4d(&tmdO, a.dO, bf, 2, a.Bm, Hq, a.Nq, DR, a.ldo.sb, a.ldo.sh, a.ldo.sn, BM, 64)) ||
+        (trc = make_tmap_4d(&tmK, a.K, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lk.sb, a.lk.sh, a.lk.sn, BN, 64)) ||
+        (trc = make_tmap_4d(&tmV, a.V, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.lv.sb, a.lv.sh, a.lv.sn, BN, 64)) ||
+        (trc = make_tmap_4d(&tmdK, a.dK, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldk.sb, a.ldk.sh, a.ldk.sn, BN, 64)) ||
+        (trc = make_tmap_4d(&tmdV, a.dV, bf, 2, a.Bm, a.Hkv, a.Nkv, DR, a.ldv.sb, a.ldv.sh, a.ldv.sn, BN, 64)))
+        return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nkv + BN - 1) / BN, a.Hkv, a.Bm);
 #ifdef B200_EXPERIMENTS
     static int dbg = -1;                     // timing-only hooks, side libraries only (see B200_DBG above)
@@ -649,7 +589,7 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 #else
     const int dbg = 0;
 #endif
-    bwd_kernel<DR, ISSUE><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
+    bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
                                                 a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
                                                 a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
     B200_CUDA_TRY(cudaGetLastError());
@@ -657,27 +597,8 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
     return B200_OK;
 }
 
-#ifdef B200_EXPERIMENTS
-// side libraries only: B200_BWD_VARIANT=2 selects the interleaved issue order (r2: correct, 8 % slower -- the kernel is
-// bound by shared-memory traffic, not by the order of its MMAs: profiles/r2a_bwd_interleaved_negative.txt)
-static int bwd_variant()
-{
-    static int variant = -1;
-    if (variant < 0) { const char* e = getenv("B200_BWD_VARIANT"); variant = e ? atoi(e) : 0; }
-    return variant;
-}
-static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st)
-{
-    return bwd_variant() == 2 ? bwd_launch<128, 2>(a, st) : bwd_launch<128>(a, st);
-}
-static int bwd_launch_d64(const BwdLaunch& a, cudaStream_t st)
-{
-    return bwd_variant() == 2 ? bwd_launch<64, 2>(a, st) : bwd_launch<64>(a, st);
-}
-#else
 static int bwd_launch_d128(const BwdLaunch& a, cudaStream_t st) { return bwd_launch<128>(a, st); }
 static int bwd_launch_d64(const BwdLaunch& a, cudaStream_t st) { return bwd_launch<64>(a, st); }
-#endif
 
 // contiguous [BH, N, 128 or 64] slabs (the reference layout); BH is cut into (batches x heads) that fit the grid limits
 static BwdLaunch contiguous_launch(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,

@@ -77,6 +77,10 @@ bool fwd_pair_eligible(const FwdArgs& a);                                // expe
 int launch_fwd_pair(const FwdArgs& a, int BH_valid, cudaStream_t st);    //   bf16 d = 128 non-causal, Nq % 512 == 0, Nkv % 128 == 0
 int launch_fwd_shs(const FwdArgs& a, int BH_valid, cudaStream_t st);     // experimental variant (fwd_shs_sm100.cu), bf16 d = 128
 int launch_fwd_dbuf(const FwdArgs& a, int BH_valid, cudaStream_t st);    // the shipped bf16 d = 128 forward (fwd_dbuf_sm100.cu)
+// persistent ring forward (fwd_dbuf_sm100.cu, RING = true): one launch walks all P K/V blocks, waiting on arrival counters
+bool fwd_ring_persistent_supported(int dtype, int d, int BH, int Nl, int nranks);
+int launch_fwd_ring_persistent(const void* Q, const void* K, const void* V, void* O, float* L, const void* Kslots, const void* Vslots,
+                               const uint32_t* flags, uint32_t epoch, int BH, int Nl, int nranks, float scale, cudaStream_t st);
 bool tc_bwd_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_workspace_bytes(int BH, int Nq, int Nkv, int d, int dtype);
 int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,

@@ -221,11 +221,41 @@ __device__ __forceinline__ void dbuf_softmax_role(int t, uint32_t tmem, uint8_t*
 
 // PEEL (B200_DBUF_PEEL=1, NOT yet run on a GPU): the issuers' steady-state iterations without any data-dependent branch
 // between two runs of MMAs (see the note at the loop).  PEEL = false is the build all r1(d) measurements were taken on.
-template <int POLY, bool PEEL>
+//
+// RING = true: the PERSISTENT RING FORWARD ("one persistent kernel across all ring steps waiting on arrival
+// flags"; replaces the reference's per-step relaunch + cudaDeviceSynchronize,
+// src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:197-226).  The key sequence of this rank's queries is
+// the concatenation of P = ring.blocks K/V blocks of ring.tiles_per_block tiles each: block 0 is the local shard (tmK /
+// tmV), block s >= 1 sits in receive slot s - 1 of the rank's scratch (tmK2 / tmV2: the slot is the outermost map
+// dimension) and is being pushed there by the previous rank's copy engine while this kernel runs.  Only the TMA
+// producer knows: before the first tile of block s it polls the arrival counter ring.flags[s] (ld.acquire.sys) until it
+// reaches ring.epoch.  MMA issuers and softmax warps see one long key loop, so (m, l, O) are carried in registers /
+// TMEM across the blocks: no partial outputs, no LSE merge, one launch per call.
+struct RingWalk { const uint32_t* flags; uint32_t epoch; int blocks, tiles_per_block; };
+
+__device__ __forceinline__ void ring_wait_block(const uint32_t* flag, uint32_t epoch)
+{
+    uint32_t v;
+    long long t0 = 0;
+    for (uint32_t polls = 0;; ++polls) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if ((int32_t)(v - epoch) >= 0) break;
+        __nanosleep(200);
+        if ((polls & 0x3FFFu) == 0x3FFFu) {                 // watchdog (~20 s): a lost peer must not hang the GPU for good
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 40000000000ll) { printf("b200attn: ring block never arrived (flag %u, want %u)\n", v, epoch); __trap(); }
+        }
+    }
+    asm volatile("fence.proxy.async;" ::: "memory");        // the block was written by a peer's DMA: order the TMA reads behind the flag
+}
+
+template <int POLY, bool PEEL, bool RING = false>
 __global__ void __launch_bounds__(fdb::THREADS, 1)
 fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                float* __restrict__ Lout, long long ldL, int Nq, int Nkv, float scale_log2, int causal, int G, int BH)
+                float* __restrict__ Lout, long long ldL, int Nq, int Nkv, float scale_log2, int causal, int G, int BH,
+                const __grid_constant__ CUtensorMap tmK2, const __grid_constant__ CUtensorMap tmV2, RingWalk ring)
 {
     using namespace fdb;
     extern __shared__ uint8_t smem_raw[];
@@ -264,6 +294,7 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int s = 0; s < ST; ++s) { mbar_init(&bar_Kf[s], 1); mbar_init(&bar_Ke[s], ntiles); mbar_init(&bar_Vf[s], 1); mbar_init(&bar_Ve[s], ntiles); }
         fence_mbar_init();
         tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
+        if constexpr (RING) { tma_prefetch_desc(&tmK2); tma_prefetch_desc(&tmV2); }
     }
     if (warp == 2) { tmem_alloc<512>(tmem_slot); tmem_relinquish(); }
     tc_fence_before();
@@ -281,19 +312,37 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     tma_load_4d(sQ + t * Q_TILE + bx * Q_BOX, &tmQ, &bar_Q[t], bx * 64, q0 + t * 128, h, b, kEvictFirst);
             }
             // order K(0) K(1) V(0) K(2) V(1) ...: the score MMAs run two tiles ahead of the PV MMAs
+            int arrived = 0;                                    // RING: blocks 0 .. arrived are known to be in place
             auto load_K = [&](int j) {
                 const int s = j % ST;
                 mbar_wait(&bar_Ke[s], ((j / ST) & 1) ^ 1);
                 mbar_expect_tx(&bar_Kf[s], KV_TILE);
-                for (int bx = 0; bx < 2; ++bx)
-                    tma_load_4d(sK + s * KV_TILE + bx * KV_BOX, &tmK, &bar_Kf[s], bx * 64, j * BC, hk, b, kEvictLast);
+                if constexpr (RING) {
+                    const int blk = j / ring.tiles_per_block, row = (j - blk * ring.tiles_per_block) * BC;
+                    if (blk > arrived) { ring_wait_block(ring.flags + blk, ring.epoch); arrived = blk; }   // (K runs ahead of V)
+                    for (int bx = 0; bx < 2; ++bx) {
+                        if (blk == 0) tma_load_4d(sK + s * KV_TILE + bx * KV_BOX, &tmK, &bar_Kf[s], bx * 64, row, hk, b, kEvictLast);
+                        else tma_load_4d(sK + s * KV_TILE + bx * KV_BOX, &tmK2, &bar_Kf[s], bx * 64, row, bh, blk - 1, kEvictLast);
+                    }
+                } else {
+                    for (int bx = 0; bx < 2; ++bx)
+                        tma_load_4d(sK + s * KV_TILE + bx * KV_BOX, &tmK, &bar_Kf[s], bx * 64, j * BC, hk, b, kEvictLast);
+                }
             };
             auto load_V = [&](int j) {
                 const int s = j % ST;
                 mbar_wait(&bar_Ve[s], ((j / ST) & 1) ^ 1);
                 mbar_expect_tx(&bar_Vf[s], KV_TILE);
-                for (int bx = 0; bx < 2; ++bx)
-                    tma_load_4d(sV + s * KV_TILE + bx * KV_BOX, &tmV, &bar_Vf[s], bx * 64, j * BC, hk, b, kEvictLast);
+                if constexpr (RING) {
+                    const int blk = j / ring.tiles_per_block, row = (j - blk * ring.tiles_per_block) * BC;
+                    for (int bx = 0; bx < 2; ++bx) {
+                        if (blk == 0) tma_load_4d(sV + s * KV_TILE + bx * KV_BOX, &tmV, &bar_Vf[s], bx * 64, row, hk, b, kEvictLast);
+                        else tma_load_4d(sV + s * KV_TILE + bx * KV_BOX, &tmV2, &bar_Vf[s], bx * 64, row, bh, blk - 1, kEvictLast);
+                    }
+                } else {
+                    for (int bx = 0; bx < 2; ++bx)
+                        tma_load_4d(sV + s * KV_TILE + bx * KV_BOX, &tmV, &bar_Vf[s], bx * 64, j * BC, hk, b, kEvictLast);
+                }
             };
             load_K(0);
             if (nkv > 1) load_K(1);
@@ -436,20 +485,60 @@ static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(fwd_dbuf_kernel<POLY, PEEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        B200_CUDA_TRY(cudaFuncSetAttribute(fwd_dbuf_kernel<POLY, PEEL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     const float scale_log2 = a.scale * 1.4426950408889634f;
     CUtensorMap tmQ, tmK, tmV, tmO;
-    if (make_tmap_4d(&tmQ, a.Q, dt, 2, a.B, a.H, a.Nq, D, a.lq.sb, a.lq.sh, a.lq.sn, 128, 64) ||
-        make_tmap_4d(&tmK, a.K, dt, 2, a.B, a.Hkv, a.Nkv, D, a.lk.sb, a.lk.sh, a.lk.sn, BC, 64) ||
-        make_tmap_4d(&tmV, a.V, dt, 2, a.B, a.Hkv, a.Nkv, D, a.lv.sb, a.lv.sh, a.lv.sn, BC, 64) ||
-        make_tmap_4d(&tmO, a.O, dt, 2, a.B, a.H, a.Nq, D, a.lo.sb, a.lo.sh, a.lo.sn, 128, 64))
-        return B200_ERR_CUDA;
+    int trc = 0;
+    if ((trc = make_tmap_4d(&tmQ, a.Q, dt, 2, a.B, a.H, a.Nq, D, a.lq.sb, a.lq.sh, a.lq.sn, 128, 64)) ||
+        (trc = make_tmap_4d(&tmK, a.K, dt, 2, a.B, a.Hkv, a.Nkv, D, a.lk.sb, a.lk.sh, a.lk.sn, BC, 64)) ||
+        (trc = make_tmap_4d(&tmV, a.V, dt, 2, a.B, a.Hkv, a.Nkv, D, a.lv.sb, a.lv.sh, a.lv.sn, BC, 64)) ||
+        (trc = make_tmap_4d(&tmO, a.O, dt, 2, a.B, a.H, a.Nq, D, a.lo.sb, a.lo.sh, a.lo.sn, 128, 64)))
+        return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nq + NT * 128 - 1) / (NT * 128), a.H, a.B);
-    fwd_dbuf_kernel<POLY, PEEL><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
-                                                       a.H / a.Hkv, BH_valid);
+    fwd_dbuf_kernel<POLY, PEEL, false><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
+                                                       a.H / a.Hkv, BH_valid, tmK, tmV, RingWalk{nullptr, 0u, 1, 0});
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
+// Persistent ring forward: contiguous [BH, Nl, 128] bf16 shards; K/V blocks 1 .. P-1 in `Kslots` / `Vslots`
+// ([P-1][BH][Nl][128], filled by the copy engines while the kernel runs); flags[s] reaches `epoch` when block s is in.
+bool fwd_ring_persistent_supported(int dtype, int d, int BH, int Nl, int nranks)
+{
+    return dtype == B200_DTYPE_BF16 && d == fdb::D && Nl >= fdb::BC && Nl % fdb::BC == 0 && BH >= 1 && BH <= 65535 && nranks >= 2 &&
+           nranks <= 256;
+}
+int launch_fwd_ring_persistent(const void* Q, const void* K, const void* V, void* O, float* L, const void* Kslots, const void* Vslots,
+                               const uint32_t* flags, uint32_t epoch, int BH, int Nl, int nranks, float scale, cudaStream_t st)
+{
+    using namespace fdb;
+    auto* kern = fwd_dbuf_kernel<4, false, true>;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const Lay lay = lay_contiguous(BH, Nl, D);
+    const uint64_t slot = (uint64_t)BH * Nl * D;                 // elements between two receive slots
+    CUtensorMap tmQ, tmK, tmV, tmO, tmK2, tmV2;
+    int trc = 0;
+    if ((trc = make_tmap_4d(&tmQ, Q, dt, 2, 1, BH, Nl, D, lay.sb, lay.sh, lay.sn, 128, 64)) ||
+        (trc = make_tmap_4d(&tmK, K, dt, 2, 1, BH, Nl, D, lay.sb, lay.sh, lay.sn, BC, 64)) ||
+        (trc = make_tmap_4d(&tmV, V, dt, 2, 1, BH, Nl, D, lay.sb, lay.sh, lay.sn, BC, 64)) ||
+        (trc = make_tmap_4d(&tmO, O, dt, 2, 1, BH, Nl, D, lay.sb, lay.sh, lay.sn, 128, 64)) ||
+        (trc = make_tmap_4d(&tmK2, Kslots, dt, 2, nranks - 1, BH, Nl, D, slot, lay.sh, lay.sn, BC, 64)) ||
+        (trc = make_tmap_4d(&tmV2, Vslots, dt, 2, nranks - 1, BH, Nl, D, slot, lay.sh, lay.sn, BC, 64)))
+        return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;
+    dim3 grid((Nl + NT * 128 - 1) / (NT * 128), BH, 1);
+    kern<<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, L, (long long)Nl, Nl, nranks * Nl, scale * 1.4426950408889634f, 0, 1, BH,
+                                      tmK2, tmV2, RingWalk{flags, epoch, nranks, Nl / BC});
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;

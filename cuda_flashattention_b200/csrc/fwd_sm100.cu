@@ -495,11 +495,12 @@ static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
     const CUtensorMapSwizzle v_swz = C::kF32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     const float scale_log2 = a.scale * 1.4426950408889634f;
     CUtensorMap tmQ, tmK, tmV, tmO;
-    if (make_tmap_4d(&tmQ, a.Q, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lq.sb, a.lq.sh, a.lq.sn, 128, C::CPB) ||
-        make_tmap_4d(&tmK, a.K, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lk.sb, a.lk.sh, a.lk.sn, C::BC, C::CPB) ||
-        make_tmap_4d(&tmV, a.V, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lv.sb, a.lv.sh, a.lv.sn, C::BC, C::CPB, v_swz) ||
-        make_tmap_4d(&tmO, a.O, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::CPB))
-        return B200_ERR_CUDA;
+    int trc = 0;
+    if ((trc = make_tmap_4d(&tmQ, a.Q, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lq.sb, a.lq.sh, a.lq.sn, 128, C::CPB)) ||
+        (trc = make_tmap_4d(&tmK, a.K, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lk.sb, a.lk.sh, a.lk.sn, C::BC, C::CPB)) ||
+        (trc = make_tmap_4d(&tmV, a.V, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lv.sb, a.lv.sh, a.lv.sn, C::BC, C::CPB, v_swz)) ||
+        (trc = make_tmap_4d(&tmO, a.O, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::CPB)))
+        return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nq + C::NT * 128 - 1) / (C::NT * 128), a.H, a.B);
     fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
                                                      a.H / a.Hkv, BH_valid);

@@ -105,11 +105,15 @@ static bool load_memops()
     return true;
 }
 
-enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_CALL_DONE = 8, F_COUNT = 16 };
+// F_PRDY + s: persistent forward -- block s of the current call has landed in receive slot s - 1 (value = call epoch)
+enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_CALL_DONE = 8, F_PRDY = 16, F_COUNT = 16 + 256 };
 
 // transport preference (b200_ring_set_transport): -1 = B200_RING_TRANSPORT decides (default: copy engines), 0 = copy engines,
 // 1 = NCCL send/recv.  Collective like the ring calls themselves: every rank holds the same value.
 static int g_transport_pref = -1;
+// forward schedule (b200_ring_set_forward_mode): 0 = automatic, 1 = one launch per ring step + n-way LSE merge,
+// 2 = one persistent launch that walks all blocks (needs the copy-engine transport; else falls back to 1)
+static int g_fwd_mode = 0;
 
 struct PeerLink {
     ncclComm_t comm = nullptr;
@@ -124,6 +128,7 @@ struct PeerLink {
     size_t exported = 0;                    // scratch size the neighbours have mapped
     void* exported_ptr = nullptr;           // ... and its address (an NCCL-transport call may have re-allocated it since)
     uint32_t calls_done = 0;                // ring calls finished on this link (F_CALL_DONE handshake)
+    uint32_t pers_epoch = 0;                // persistent forward calls made on this link (value of their arrival flags)
     uint32_t push_kv[2] = {0, 0}, in_kv[2] = {0, 0}, rel_kv[2] = {0, 0};
     uint32_t push_acc[2] = {0, 0}, in_acc[2] = {0, 0}, out_acc[2] = {0, 0};
 };
@@ -385,6 +390,13 @@ int b200_ring_set_transport(int mode)
     return B200_OK;
 }
 
+int b200_ring_set_forward_mode(int mode)
+{
+    if (mode < 0 || mode > 2) return B200_ERR_INVALID_ARGUMENT;
+    g_fwd_mode = mode;
+    return B200_OK;
+}
+
 int b200_ring_unique_id(void* out128)
 {
     if (!out128) return B200_ERR_INVALID_ARGUMENT;
@@ -459,6 +471,51 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t kv_bytes = (size_t)B * H * Nl * d * es;
     const size_t l_bytes = (size_t)B * H * Nl * sizeof(float);
+
+    // ---- persistent forward: every block gets its OWN receive slot, the copy engines forward block after
+    // block around the ring with no reference to the compute (push s waits only for arrival s), and ONE attention
+    // launch walks the blocks in arrival order, its TMA producer polling the arrival counters the pushes write.  No
+    // per-step launches, no partial outputs, no merge kernel; the kernel never waits on a kernel of another rank, only
+    // on copy-engine traffic that is independent of every SM.
+    {
+        const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
+        const bool want = g_fwd_mode != 1 && !causal && (long long)B * H <= 65535 && (al & 15) == 0 &&
+                          fwd_ring_persistent_supported(dtype, d, B * H, Nl, nranks) && nranks <= 256;
+        if (want) {
+            const size_t need = 2 * (size_t)(nranks - 1) * kv_bytes;      // (kv_bytes is a multiple of 16 KB here)
+            void* base;
+            bool ce = false;
+            B200_TRY(link_prepare(rs, comm, rank, nranks, need, &base, &ce));
+            if (ce) {
+                int dev = 0;
+                B200_CUDA_TRY(cudaGetDevice(&dev));
+                PeerLink& lk = g_link[dev];
+                uint8_t* Ks = reinterpret_cast<uint8_t*>(base);
+                uint8_t* Vs = Ks + (size_t)(nranks - 1) * kv_bytes;
+                const uint32_t epoch = ++lk.pers_epoch;
+                const float sc = scale > 0.0f ? scale : 1.0f / sqrtf((float)d);
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
+                B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+                B200_TRY(call_begin(lk, rs));
+                for (int s = 0; s + 1 < nranks; ++s) {
+                    // block s (the local shard for s = 0, else what arrived in slot s - 1) goes into the next rank's slot s
+                    if (s >= 1) B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_PRDY + s, epoch));
+                    const void* ks = s == 0 ? K : (const void*)(Ks + (size_t)(s - 1) * kv_bytes);
+                    const void* vs = s == 0 ? V : (const void*)(Vs + (size_t)(s - 1) * kv_bytes);
+                    B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + (size_t)s * kv_bytes, ks, kv_bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
+                    B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + (size_t)(nranks - 1 + s) * kv_bytes, vs, kv_bytes, cudaMemcpyDeviceToDevice,
+                                                  rs->comm_stream));
+                    B200_TRY(write_val(rs->comm_stream, lk.next_flags + F_PRDY + s + 1, epoch));
+                }
+                B200_TRY(launch_fwd_ring_persistent(Q, K, V, O, L, Ks, Vs, lk.flags + F_PRDY, epoch, B * H, Nl, nranks, sc, st));
+                // the caller may reuse K/V (the source of the first push) once its stream has passed this call
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
+                B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
+                B200_TRY(call_end(lk, rs, st));
+                return B200_OK;
+            }
+        }
+    }
     // scratch: 2 x (K,V) receive buffers + NB x (partial O + partial LSE).  One partial per ring step when that fits
     // in 4 GB (it does for every shape in BASELINE.json): no step then waits for a merge -- they are all folded by one
     // n-way merge at the end -- and each attention kernel can start in the tail of the previous one.

@@ -76,6 +76,19 @@ B200_API int b200_version(void);
 B200_API int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
 B200_API int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
 
+/* The same question for ONE CONCRETE CALL: which family b200_fa2_fwd(_ex) / b200_fa2_bwd(_ex) will run with these
+ * pointers, shape, scale and flags.  Beyond (dtype, d) the tensor-core kernels need 16-byte aligned base pointers (TMA),
+ * scale > 0 after the "0 means 1/sqrt(d)" rule (forward), and -- for B200_FLAG_CAUSAL -- a square problem; a call that
+ * misses one of these still runs, on the generic CUDA-core kernels (~15 TFLOP/s), and this is how a caller finds out.
+ * Returns B200_ROUTE_TENSOR_CORE, B200_ROUTE_GENERIC or a negative b200_status for arguments the call would reject.
+ * Pure host functions (no device needed); the calls themselves use exactly these predicates. */
+#define B200_ROUTE_GENERIC 0
+#define B200_ROUTE_TENSOR_CORE 1
+B200_API int b200_fa2_fwd_route(const void* Q, const void* K, const void* V, const void* O, int Nq, int Nkv, int d,
+                       float scale, int dtype, int flags);
+B200_API int b200_fa2_bwd_route(const void* Q, const void* K, const void* V, const void* dO, const void* dQ, const void* dK,
+                       const void* dV, int Nq, int Nkv, int d, float scale, int dtype, int flags);
+
 /* Test hook: non-zero routes every call to the generic CUDA-core kernels (used by the GPU tests to
  * cross-check the tensor-core kernels on the device at sizes the CPU oracle cannot reach).
  * Returns the previous setting.  Not a fallback: both families are GPU code in this library. */
@@ -234,6 +247,16 @@ B200_API int b200_ring_bwd_ex(const void* Q_local, const void* K_local, const vo
 /* chunk index (0 .. 2P-1) held in half `half` (0 / 1) of rank `rank`'s local rows under the zigzag sharding */
 B200_API int b200_ring_zigzag_chunk(int rank, int half, int nranks);
 
+/* Host-buffer ring call: the reference's ring driver owns HOST arrays and copies its shard to the device around the call
+ * (src/03_flash_attention_v2_ring/04_ring_attention.cu:97-112).  This does the same for [B,H,N_local,d] host shards
+ * (pinned memory for full speed), pipelined like b200_fa2_fwd_bwd_host: the (b,h) slabs are cut into >= 2 chunks and the
+ * host->device copy, ring forward + backward and device->host copy of consecutive chunks overlap.  Collective (every
+ * rank calls it with the same shapes); stream-ordered on `stream`. */
+B200_API int b200_ring_fwd_bwd_host(const void* hQ, const void* hK, const void* hV, const void* hdO,
+                           void* hO, float* hL, void* hdQ, void* hdK, void* hdV,
+                           int B, int H, int N_local, int d, float scale, int dtype, int flags,
+                           ncclComm_t comm, int rank, int nranks, cudaStream_t stream);
+
 /* NCCL bootstrap without MPI (replaces init_nccl_comm / cleanup_mpi_nccl, src/util/nccl_utils.h:29-103):
  * rank 0 calls b200_ring_unique_id and ships the 128 bytes to the other ranks by any means
  * (file, env, torch.distributed store), then every rank calls b200_ring_comm_init. */
@@ -255,6 +278,22 @@ B200_API int b200_ring_exchange_kv(const void* send_k, void* recv_k, const void*
 #define B200_RING_TRANSPORT_COPY_ENGINE 0
 #define B200_RING_TRANSPORT_NCCL 1
 B200_API int b200_ring_set_transport(int mode);
+
+/* Schedule of the ring FORWARD:
+ *   B200_RING_FWD_AUTO (0, default)  : PERSISTENT when the shape allows it (bf16, d = 128, N_local a multiple of 64,
+ *       non-causal, copy-engine transport usable), else STEPWISE;
+ *   B200_RING_FWD_STEPWISE (1)       : one attention launch per ring step into its own partial (O_s, LSE_s), one n-way
+ *       log-sum-exp merge at the end -- the reference's schedule (common/ring_attention_kernel.cu:197-226) without its
+ *       per-step cudaDeviceSynchronize;
+ *   B200_RING_FWD_PERSISTENT (2)     : ONE launch per call.  Every K/V block has its own receive slot, the copy engines
+ *       forward the blocks around the ring independently of the compute, and the kernel's TMA producer waits on the
+ *       arrival counters they write, carrying (m, l, O) across the blocks in registers / TMEM (device-side
+ *       waiting instead of host-sequenced steps; no partial buffers, no merge).
+ * Collective like b200_ring_set_transport. */
+#define B200_RING_FWD_AUTO 0
+#define B200_RING_FWD_STEPWISE 1
+#define B200_RING_FWD_PERSISTENT 2
+B200_API int b200_ring_set_forward_mode(int mode);
 
 /* Frees the library's per-device scratch arena (optional; also released at process exit). */
 B200_API int b200_release_workspace(void);

@@ -14,6 +14,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libnaive_oracle.so")
 _REF = os.path.join(_HERE, "_ref", "libref_naive.so")
+_REF_CUDA_FWD = os.path.join(_HERE, "_ref", "libref_cuda_fwd.so")
+_REF_CUDA_BWD = os.path.join(_HERE, "_ref", "libref_cuda_bwd.so")
 
 _fp = C.POINTER(C.c_float)
 _dp = C.POINTER(C.c_double)
@@ -26,6 +28,10 @@ def build(force=False):
         subprocess.check_call(["make", "-C", _HERE, "libnaive_oracle.so"], stdout=subprocess.DEVNULL)
     if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF)):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF_CUDA_FWD) or not os.path.exists(_REF_CUDA_BWD)):
+        import shutil
+        if shutil.which("nvcc"):
+            subprocess.check_call(["make", "-C", _HERE, "refcuda"], stdout=subprocess.DEVNULL)
 
 
 _lib = None
@@ -223,3 +229,35 @@ def ref_fixture(name, n_elems):
     fn = getattr(ref(), "ref_fixture_" + name)
     fn(*[a.ctypes.data_as(_fp) for a in arrs], C.c_int(n_elems))
     return arrs
+
+
+# ---- the unmodified reference CUDA kernels (oracle/_ref/libref_cuda_*.so, built by `make refcuda`) ----------------
+# Device-pointer calls on torch CUDA float32 tensors [N, d]; they launch on the legacy default stream like the
+# reference wrappers do and return cudaGetLastError().  d <= 64 only (reference assert).
+_ref_cuda = {}
+
+
+def ref_cuda_available():
+    return os.path.exists(_REF_CUDA_FWD) and os.path.exists(_REF_CUDA_BWD)
+
+
+def _ref_cuda_lib(which):
+    if which not in _ref_cuda:
+        _ref_cuda[which] = C.CDLL(_REF_CUDA_FWD if which == "fwd" else _REF_CUDA_BWD)
+    return _ref_cuda[which]
+
+
+def ref_cuda_forward(Q, K, V, O, L, scale):
+    """flash_attention_2_forward, reference src/03_flash_attention_v2_ring/common/flash_attention_kernel.cu:133-172."""
+    N, d = Q.shape
+    vp = C.c_void_p
+    return int(_ref_cuda_lib("fwd").ref_cuda_fa2_forward(vp(Q.data_ptr()), vp(K.data_ptr()), vp(V.data_ptr()), vp(O.data_ptr()),
+                                                         vp(L.data_ptr()), C.c_int(N), C.c_int(d), C.c_float(scale)))
+
+
+def ref_cuda_backward(Q, K, V, O, L, dO, dQ, dK, dV, scale):
+    """flash_attention_2_backward, reference src/02_flash_attention_v2_backward/flash_attention_backward_kernel.cu:249-299."""
+    N, d = Q.shape
+    vp = C.c_void_p
+    return int(_ref_cuda_lib("bwd").ref_cuda_fa2_backward(*[vp(t.data_ptr()) for t in (Q, K, V, O, L, dO, dQ, dK, dV)],
+                                                          C.c_int(N), C.c_int(d), C.c_float(scale)))

@@ -9,6 +9,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import oracle  # noqa: E402
 import cuda_flashattention_b200 as fa  # noqa: E402
+from cuda_flashattention_b200._lib import lib, check  # noqa: E402
 
 
 def main():
@@ -17,7 +18,30 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     comm = fa.RingComm()
     ok = True
-    for (dtype, H, N, d, tol) in ((torch.bfloat16, 2, 256 * world, 128, 2e-2), (torch.float32, 1, 5096 // world * world, 64, 2e-3)):
+    # every data plane / forward schedule the library has (include/b200attn.h: b200_ring_set_transport,
+    # b200_ring_set_forward_mode): copy engines + persistent forward (the default), copy engines + one launch per step,
+    # NCCL send/recv (the reference's ring_exchange_kv; always stepwise)
+    for (transport, fwd_mode, label) in ((0, 2, "copy-engine/persistent"), (0, 1, "copy-engine/stepwise"), (1, 1, "nccl/stepwise")):
+        check(lib.b200_ring_set_transport(transport), "set_transport")
+        check(lib.b200_ring_set_forward_mode(fwd_mode), "set_forward_mode")
+        if rank == 0:
+            print("=== ring configuration:", label)
+        ok = battery(rank, world, comm) and ok
+    check(lib.b200_ring_set_transport(-1), "set_transport")
+    check(lib.b200_ring_set_forward_mode(0), "set_forward_mode")
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    comm.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("RING_OK" if flag.item() == 1 else "RING_FAIL")
+    sys.exit(0 if flag.item() == 1 else 1)
+
+
+def battery(rank, world, comm):
+    ok = True
+    for (dtype, H, N, d, tol) in ((torch.bfloat16, 2, 256 * world, 128, 2e-2), (torch.bfloat16, 3, 448 * world, 128, 2e-2),
+                                  (torch.float32, 1, 5096 // world * world, 64, 2e-3)):
         rng = np.random.default_rng(7)
         Q, K, V, dO = [rng.standard_normal((1, H, N, d)).astype(np.float32) for _ in range(4)]
         n = N // world
@@ -66,13 +90,7 @@ def main():
             if rank == 0:
                 print("causal zigzag", dtype, "head", h, {k_: float(v_) for k_, v_ in errs.items()})
             ok = ok and all(e <= tol for e in errs.values())
-    flag = torch.tensor([1 if ok else 0], device="cuda")
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    comm.close()
-    dist.destroy_process_group()
-    if rank == 0:
-        print("RING_OK" if flag.item() == 1 else "RING_FAIL")
-    sys.exit(0 if flag.item() == 1 else 1)
+    return ok
 
 
 if __name__ == "__main__":

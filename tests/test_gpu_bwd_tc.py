@@ -28,11 +28,14 @@ def _check(Nq, Nkv, d, seed, qscale=1.0, B=1, H=1):
             ref = oracle.backward(host(q[b, h]), host(k[b, h]), host(v[b, h]), host(do[b, h]), 0.0)
             for name, got, want in zip(("dQ", "dK", "dV"), (dQ, dK, dV), ref):
                 g = host(got[b, h])
-                e = (float(np.abs(g - want).max()), rel_l2(g, want))
+                # max-abs in units of THIS tensor's own reference magnitude when that exceeds 1 (the "peaky" case scales Q
+                # by 3, its gradients reach |dK| ~ 10): the literal 2e-2 for unit-scale data
+                e = (float(np.abs(g - want).max()) / max(1.0, float(np.abs(want).max())), rel_l2(g, want))
                 worst[name] = max(worst.get(name, (0, 0)), e)
     print(Nq, Nkv, worst)
+    # north_star's bf16 bound, literally, per tensor against its own reference (unit-scale inputs)
     for name, (mx, rl) in worst.items():
-        assert mx <= 2e-2 * max(1.0, float(np.abs(want).max())), (name, mx)
+        assert mx <= 2e-2, (name, mx)
         assert rl <= 1e-2, (name, rl)
 
 
@@ -75,3 +78,34 @@ def test_bwd_large_against_generic():
         rl = ((a.float() - b.float()).norm() / b.float().norm()).item()
         print(name, err, rl)
         assert err <= 2e-2 and rl <= 1e-2
+
+
+def test_c3_shape_sampled_rows_vs_oracle():
+    """BASELINE config C3's shape (N = 8192, d = 128: 64 K/V tiles per forward CTA, 128 q-tile iterations per backward
+    CTA) against the CPU oracle: O, L, dQ on sampled query rows and dK, dV on sampled key rows of two heads, with the
+    per-row statistics computed by the oracle itself (oracle.row_stats) -- the gate bench.py also applies to its own
+    timed outputs.  Size-independent identities cover every element: colsum(dV) = colsum(dO), colsum(dK) = 0."""
+    rng = np.random.default_rng(8192)
+    B, H, N, d = 1, 2, 8192, 128
+    q, k, v = [dev(rng.standard_normal((B, H, N, d)).astype(np.float32), torch.bfloat16) for _ in range(3)]
+    do = dev(0.2 * rng.standard_normal((B, H, N, d)).astype(np.float32), torch.bfloat16)
+    O, L = fa.flash_attention_2_forward(q, k, v, 0.0)
+    dQ, dK, dV = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0)
+    edge = [0, 63, 64, 127, 128, N - 129, N - 128, N - 1]
+    for h in range(H):
+        qrows = np.unique(np.concatenate([edge, rng.integers(0, N, 16)])).astype(np.int32)
+        kvrows = np.unique(np.concatenate([edge, rng.integers(0, N, 16)])).astype(np.int32)
+        Q_, K_, V_, dO_ = host(q[0, h]), host(k[0, h]), host(v[0, h]), host(do[0, h])
+        Oo, Lo = oracle.forward_rows(Q_, K_, V_, qrows, 0.0)
+        gq, gk, gv = oracle.backward_rows(Q_, K_, V_, dO_, qrows, kvrows, 0.0)
+        for name, got, want in (("O", host(O[0, h])[qrows], Oo), ("L", host(L[0, h])[qrows], Lo), ("dQ", host(dQ[0, h])[qrows], gq),
+                                ("dK", host(dK[0, h])[kvrows], gk), ("dV", host(dV[0, h])[kvrows], gv)):
+            mx = float(np.abs(got - want).max())
+            print(h, name, mx, rel_l2(got, want))
+            assert mx <= 2e-2, (name, mx)
+            if name != "L":
+                assert rel_l2(got, want) <= 1e-2, (name, rel_l2(got, want))
+    u = 8.0 * 2.0 ** -8
+    sdv, sdo, sdk = dV.double().sum(2), do.double().sum(2), dK.double().sum(2)
+    assert ((sdv - sdo).abs() <= u * ((dV.double() ** 2).sum(2) + (do.double() ** 2).sum(2)).sqrt()).all()
+    assert (sdk.abs() <= u * (dK.double() ** 2).sum(2).sqrt()).all()

@@ -122,6 +122,25 @@ def test_autograd_function_matches_a_float32_torch_reference():
         assert (got.float() - want).abs().max().item() <= 2e-2 * max(1.0, want.abs().max().item())
 
 
+def test_autograd_expanded_gradient_is_not_read_as_contiguous():
+    """O.sum().backward() hands the backward a gradient expanded over every dimension (all strides 0).  The all-zero
+    layout means "contiguous [B,H,N,d]" in the C-ABI, so the host mirror has to materialise it."""
+    B, N, H, d = 1, 192, 2, 128
+    q, k, v = _rand((B, N, H, d), 11), _rand((B, N, H, d), 12), _rand((B, N, H, d), 13)
+    qa, ka, va = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    fa.flash_attn_func(qa, ka, va).sum().backward()
+    qr, kr, vr = [t.float().clone().requires_grad_(True) for t in (q, k, v)]
+    s = torch.einsum("bqhd,bkhd->bhqk", qr, kr) / d ** 0.5
+    torch.einsum("bhqk,bkhd->bqhd", torch.softmax(s, dim=-1), vr).sum().backward()
+    for got, want in ((qa.grad, qr.grad), (ka.grad, kr.grad), (va.grad, vr.grad)):
+        assert (got.float() - want).abs().max().item() <= 2e-2
+    # a descriptor the tensor maps cannot express is UNSUPPORTED, not a CUDA error (row stride not a multiple of 16 bytes)
+    big = _rand((1, 2, 64, 132), 14)
+    with pytest.raises(fa.B200Error) as ei:
+        fa.attention_forward(big[..., 2:130], big[..., 2:130], big[..., 2:130], layout="bhnd")
+    assert ei.value.status == -8
+
+
 @pytest.mark.parametrize("causal,Hkv", [(False, 2), (True, 4), (False, 1)])
 def test_packed_variable_length_batch(causal, Hkv):
     # three sequences of different lengths in one packed [total, H, d] batch (cross lengths when not causal)

@@ -1,0 +1,125 @@
+"""The reference's own CUDA kernels beside ours on the same inputs (north_star: "checked ... against the repo's own CPU
+naive attention and its CUDA FA2/ring kernels").
+
+Runs BASELINE config C2 (FA2 forward B=1 H=8 N=4096 d=64, fp32 I/O -- the reference's type) through
+  (a) the reference's unmodified flash_attention_2_forward (03 ring/1-GPU configuration, Br = Bc = 32, 64 threads), one
+      launch per head exactly as its drivers call it, from oracle/_ref/libref_cuda_fwd.so;
+  (b) ours: b200_fa2_fwd (fp32 I/O, tf32 tcgen05 MMAs) on the batched tensor, and per head through the
+      reference-signature call b200_fa2_fwd_f32;
+and the backward at the same shape through the reference's flash_attention_2_backward and b200_fa2_bwd_f32 / b200_fa2_bwd.
+Reports max-abs differences (ours vs theirs, both vs the CPU oracle on sampled rows) and CUDA-event times.
+
+    python tools/ref_cuda_compare.py [--n 4096] [--heads 8] [--reps 20]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import oracle  # noqa: E402
+import cuda_flashattention_b200 as fa  # noqa: E402
+
+
+def timed(fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=4096)
+    ap.add_argument("--heads", type=int, default=8)
+    ap.add_argument("--d", type=int, default=64)
+    ap.add_argument("--reps", type=int, default=20)
+    a = ap.parse_args()
+    assert oracle.ref_cuda_available(), "oracle/_ref/libref_cuda_*.so missing: make -C oracle refcuda (needs /root/reference)"
+    H, N, d = a.heads, a.n, a.d
+    sc = 1.0 / d ** 0.5
+    g = torch.Generator(device="cuda").manual_seed(42)
+    # the reference's own test distribution (02_*_forward/main.cu:14-33): uniform(-0.5, 0.5); dO uniform(-0.2, 0.2)
+    mk = lambda s: (torch.rand(1, H, N, d, device="cuda", generator=g) - 0.5) * 2 * s
+    Q, K, V, dO = mk(0.5), mk(0.5), mk(0.5), mk(0.2)
+    out = {"config": f"C2-shaped: B=1 H={H} N={N} d={d} fp32 I/O, scale 1/sqrt(d), uniform(-0.5,0.5) inputs", "reps": a.reps}
+    cur = torch.cuda.current_stream()
+    legacy = torch.cuda.ExternalStream(0)          # the reference wrappers launch on the legacy default stream
+
+    # ---------------- forward
+    O_ref, L_ref = torch.empty_like(Q), torch.empty(1, H, N, device="cuda")
+    def ref_fwd():
+        for h in range(H):
+            rc = oracle.ref_cuda_forward(Q[0, h], K[0, h], V[0, h], O_ref[0, h], L_ref[0, h], sc)
+            assert rc == 0, rc
+    with torch.cuda.stream(legacy):
+        t_ref_f = timed(ref_fwd, max(2, a.reps // 4))
+    O, L = fa.flash_attention_2_forward(Q, K, V, sc)
+    t_our_f = timed(lambda: fa.flash_attention_2_forward(Q, K, V, sc), a.reps)
+    def ours_per_head():
+        for h in range(H):
+            fa.flash_attention_2_forward(Q[0, h], K[0, h], V[0, h], sc)
+    t_our_f1 = timed(ours_per_head, a.reps)
+    qb, kb, vb = Q.bfloat16(), K.bfloat16(), V.bfloat16()
+    t_our_fb = timed(lambda: fa.flash_attention_2_forward(qb, kb, vb, sc), a.reps)
+    torch.cuda.synchronize()
+    rows = np.unique(np.concatenate([[0, 31, 32, N - 1], np.random.default_rng(0).integers(0, N, 12)])).astype(np.int32)
+    h0 = H - 1
+    Oo, Lo = oracle.forward_rows(Q[0, h0].cpu().numpy(), K[0, h0].cpu().numpy(), V[0, h0].cpu().numpy(), rows, sc)
+    flops_f = 4.0 * H * N * N * d
+    out["forward"] = {
+        "reference_cuda_ms": t_ref_f, "ours_batched_tf32_ms": t_our_f, "ours_per_head_calls_tf32_ms": t_our_f1, "ours_batched_bf16_ms": t_our_fb,
+        "reference_cuda_tflops": flops_f / t_ref_f / 1e9, "ours_tf32_tflops": flops_f / t_our_f / 1e9, "ours_bf16_tflops": flops_f / t_our_fb / 1e9,
+        "speedup_tf32_vs_reference_cuda": t_ref_f / t_our_f,
+        "max_abs_O_ours_vs_reference_cuda": float((O - O_ref).abs().max()), "max_abs_L_ours_vs_reference_cuda": float((L - L_ref).abs().max()),
+        "max_abs_O_ours_vs_cpu_oracle_rows": float(np.abs(O[0, h0].cpu().numpy()[rows] - Oo).max()),
+        "max_abs_O_reference_cuda_vs_cpu_oracle_rows": float(np.abs(O_ref[0, h0].cpu().numpy()[rows] - Oo).max()),
+        "max_abs_L_ours_vs_cpu_oracle_rows": float(np.abs(L[0, h0].cpu().numpy()[rows] - Lo).max()),
+        "tolerance": "tf32 path <= 2e-3 (north_star)"}
+
+    # ---------------- backward (the reference backward reads O and L from ITS forward)
+    g_ref = [torch.empty_like(Q) for _ in range(3)]
+    def ref_bwd():
+        for h in range(H):
+            rc = oracle.ref_cuda_backward(Q[0, h], K[0, h], V[0, h], O_ref[0, h], L_ref[0, h], dO[0, h],
+                                          g_ref[0][0, h], g_ref[1][0, h], g_ref[2][0, h], sc)
+            assert rc == 0, rc
+    with torch.cuda.stream(legacy):
+        t_ref_b = timed(ref_bwd, max(2, a.reps // 4), warm=1)
+    ours = fa.flash_attention_2_backward(Q, K, V, O, L, dO, sc)
+    t_our_b = timed(lambda: fa.flash_attention_2_backward(Q, K, V, O, L, dO, sc), a.reps)
+    dob = dO.bfloat16()
+    Ob, Lb = fa.flash_attention_2_forward(qb, kb, vb, sc)
+    t_our_bb = timed(lambda: fa.flash_attention_2_backward(qb, kb, vb, Ob, Lb, dob, sc), a.reps)
+    torch.cuda.synchronize()
+    qr = rows
+    want = oracle.backward_rows(Q[0, h0].cpu().numpy(), K[0, h0].cpu().numpy(), V[0, h0].cpu().numpy(), dO[0, h0].cpu().numpy(), qr, qr, sc)
+    flops_b = 10.0 * H * N * N * d
+    out["backward"] = {
+        "reference_cuda_ms": t_ref_b, "ours_fp32_io_ms": t_our_b, "ours_bf16_ms": t_our_bb,
+        "reference_cuda_tflops": flops_b / t_ref_b / 1e9, "ours_fp32_io_tflops": flops_b / t_our_b / 1e9, "ours_bf16_tflops": flops_b / t_our_bb / 1e9,
+        "speedup_fp32_io_vs_reference_cuda": t_ref_b / t_our_b,
+        "ours_fp32_io_kernel_family": "tcgen05 (tf32)" if fa.uses_tensor_cores(torch.float32, d, N, N, backward=True) else "generic CUDA-core",
+        "max_abs_ours_vs_reference_cuda": {n: float((x - y).abs().max()) for n, x, y in zip(("dQ", "dK", "dV"), ours, g_ref)},
+        "max_abs_ours_vs_cpu_oracle_rows": {n: float(np.abs(x[0, h0].cpu().numpy()[qr] - w).max()) for n, x, w in zip(("dQ", "dK", "dV"), ours, want)},
+        "max_abs_reference_cuda_vs_cpu_oracle_rows": {n: float(np.abs(x[0, h0].cpu().numpy()[qr] - w).max()) for n, x, w in zip(("dQ", "dK", "dV"), g_ref, want)},
+        "tolerance": "fp32 I/O <= 2e-3 (north_star); the reference's own threshold on its random fixture is 5e-3"}
+    print(json.dumps(out, indent=1))
+    f, b = out["forward"], out["backward"]
+    ok = (f["max_abs_O_ours_vs_reference_cuda"] <= 2e-3 and f["max_abs_L_ours_vs_reference_cuda"] <= 2e-3 and
+          all(v <= 2e-3 for v in b["max_abs_ours_vs_reference_cuda"].values()))
+    print("REF_CUDA_COMPARE", "OK" if ok else "FAIL")
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -147,6 +147,7 @@ struct Case {
     int N, K;
     bool swap_a, swap_b;      // alternative hypothesis: swap LBO/SBO roles
     int atom32;               // MN-major operands use the 32-byte-atom 128B swizzle; value = SBO in bytes (0 = off)
+    int atomk_a, atomk_b;     // r2: a K-MAJOR operand stored with the 32-byte-atom swizzle (layout 1); value = SBO in bytes
 };
 
 int main(int argc, char** argv)
@@ -174,6 +175,14 @@ int main(int argc, char** argv)
         {"tf32 TN  SS  A MN-major ATOM_32B SBO=512    ", 4, 0, true, false, 128, 64, false, false, 512},
         {"tf32 NN  SS  N=64 V ATOM_32B SBO=512   K=128", 4, 0, false, true, 64, 128, false, false, 512},
         {"tf32 NT  TS  P in TMEM, B K-major           ", 4, 1, false, false, 128, 64, false, false, 0},
+        // r2 (tf32 backward): can ONE shared-memory tile serve as a K-major operand of one MMA and as an MN-major operand
+        // of another?  MN-major tf32 needs the ATOM_32B swizzle, so the K-major view has to read that layout too.
+        {"tf32 NT  SS  B K-major ATOM_32B SBO=1024    ", 4, 0, false, false, 128, 64, false, false, 0, 0, 1024},
+        {"tf32 NT  SS  A K-major ATOM_32B SBO=1024    ", 4, 0, false, false, 128, 64, false, false, 0, 1024, 0},
+        {"tf32 NT  SS  A,B K-major ATOM_32B SBO=1024  ", 4, 0, false, false, 128, 64, false, false, 0, 1024, 1024},
+        {"tf32 NT  SS  B K-major ATOM_32B SBO=512     ", 4, 0, false, false, 128, 64, false, false, 0, 0, 512},
+        {"tf32 NT  SS  N=64 A,B K-major ATOM_32B      ", 4, 0, false, false, 64, 64, false, false, 0, 1024, 1024},
+        {"tf32 TT  SS  N=64 A,B MN-major ATOM_32B 512 ", 4, 0, true, true, 64, 128, false, false, 512},
     };
     const int ncases = sizeof(cases) / sizeof(cases[0]);
     if (argc < 2) { printf("%d\n", ncases); return 0; }
@@ -211,8 +220,8 @@ int main(int argc, char** argv)
 
     CUtensorMap tmA, tmB;
     CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
-    CUtensorMapSwizzle swA = (c.atom32 && c.a_mn) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
-    CUtensorMapSwizzle swB = (c.atom32 && c.b_mn) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    CUtensorMapSwizzle swA = ((c.atom32 && c.a_mn) || c.atomk_a) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+    CUtensorMapSwizzle swB = ((c.atom32 && c.b_mn) || c.atomk_b) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     if (make_tmap_3d(&tmA, dA, dt, eb, 1, ar, ac, ar, cpb, swA) || make_tmap_3d(&tmB, dB, dt, eb, 1, br, bc, br, cpb, swB)) {
         printf("tensor map encode failed\n"); return 2;
     }
@@ -235,6 +244,8 @@ int main(int argc, char** argv)
     p.a_layout = 2; p.b_layout = 2;
     if (c.atom32 && c.a_mn) { p.a_layout = 1; p.a_sbo = c.atom32; }
     if (c.atom32 && c.b_mn) { p.b_layout = 1; p.b_sbo = c.atom32; }
+    if (c.atomk_a && !c.a_mn) { p.a_layout = 1; p.a_sbo = c.atomk_a; }
+    if (c.atomk_b && !c.b_mn) { p.b_layout = 1; p.b_sbo = c.atomk_b; }
     p.a_tmem_cols_per_step = 8;    // bf16: 16 K-elements packed 2/column; tf32: 8 K-elements 1/column
     p.idesc = make_idesc(eb == 2 ? kFmtBF16 : kFmtTF32, M, N, c.a_mn, c.b_mn);
 
