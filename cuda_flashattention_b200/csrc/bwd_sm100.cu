@@ -708,10 +708,24 @@ int tc_bwd_ring_step_sub(const void* Q, const void* K, const void* V, const void
     const int Nl_pad = (Nl + 63) / 64 * 64;
     const float* L2p = reinterpret_cast<const float*>(stats);
     const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + al256((size_t)BH * Nl_pad * sizeof(float)));
+    return tc_bwd_ring_step_heads(Q, K, V, dO, L2p, Dp, dQacc, dKp, dVp, 0, BH, Nl, q_row0, Nq, Nkv, causal, scale, st);
+}
+
+// ... and on a range of heads [h0, h0 + nh) of the call's B*H slabs (every pointer is the base of the WHOLE tensor; L2p / Dp
+// are the two padded statistics arrays of tc_bwd_ring_prepare).  The ring backward cuts its last step into head groups so
+// that a group's finished dK / dV accumulators travel home while the next group computes.
+int tc_bwd_ring_step_heads(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
+                           float* dQacc, void* dKp, void* dVp, int h0, int nh, int Nl, int q_row0, int Nq, int Nkv, bool causal,
+                           float scale, cudaStream_t st)
+{
+    const int Nl_pad = (Nl + 63) / 64 * 64;
     if (q_row0 != 0 && (q_row0 % 64 != 0)) return B200_ERR_UNSUPPORTED;     // statistics tiles must stay inside the slab's padding
-    const size_t qo = (size_t)q_row0 * 128;
-    BwdLaunch a = contiguous_launch(reinterpret_cast<const __nv_bfloat16*>(Q) + qo, K, V, reinterpret_cast<const __nv_bfloat16*>(dO) + qo,
-                                    L2p + q_row0, Dp + q_row0, dQacc + qo, dKp, dVp, BH, Nq, Nkv, 128, scale, causal);
+    const size_t slab = (size_t)Nl * 128, qo = (size_t)h0 * slab + (size_t)q_row0 * 128, ko = (size_t)h0 * slab;
+    const __nv_bfloat16 *Qb = reinterpret_cast<const __nv_bfloat16*>(Q), *Kb = reinterpret_cast<const __nv_bfloat16*>(K),
+                        *Vb = reinterpret_cast<const __nv_bfloat16*>(V), *dOb = reinterpret_cast<const __nv_bfloat16*>(dO);
+    BwdLaunch a = contiguous_launch(Qb + qo, Kb + ko, Vb + ko, dOb + qo, L2p + (size_t)h0 * Nl_pad + q_row0,
+                                    Dp + (size_t)h0 * Nl_pad + q_row0, dQacc + qo, reinterpret_cast<__nv_bfloat16*>(dKp) + ko,
+                                    reinterpret_cast<__nv_bfloat16*>(dVp) + ko, nh, Nq, Nkv, 128, scale, causal);
     // slabs are Nl rows apart whatever the sub-block covers
     const Lay full = lay_contiguous(a.Hkv, Nl, 128);
     a.lq = a.ldo = a.lk = a.lv = a.ldk = a.ldv = full;

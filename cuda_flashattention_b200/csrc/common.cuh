@@ -98,6 +98,10 @@ int tc_bwd_ring_step_sub(const void* Q, const void* K, const void* V, const void
                          float* dQacc, void* dKp, void* dVp, int BH, int Nl, int q_row0, int Nq, int Nkv, bool causal,
                          float scale, cudaStream_t st);
 
+int tc_bwd_ring_step_heads(const void* Q, const void* K, const void* V, const void* dO, const float* L2p, const float* Dp,
+                           float* dQacc, void* dKp, void* dVp, int h0, int nh, int Nl, int q_row0, int Nq, int Nkv, bool causal,
+                           float scale, cudaStream_t st);
+
 // ---- per-device scratch arena (api.cu) ------------------------------------------------------------
 // Grows monotonically; reuse across calls is safe because all users are stream-ordered on the
 // caller's stream and growth synchronises the device before freeing the old block.

@@ -269,13 +269,18 @@ static int ce_push_kv(PeerLink& L, RingState* rs, int slot, const void* k, const
     return write_val(rs->comm_stream, L.next_flags + F_RDY_KV + slot, n);
 }
 
-// acc[i] += (float)part[i]
-template <typename T>
-__global__ void __launch_bounds__(256) accum_kernel(float* __restrict__ acc, const T* __restrict__ part, size_t n)
+// acc[i] (+)= (float)part[i] for the PAIR of tensors selected by blockIdx.y (dK and dV in one launch).  INIT: acc = part
+// (step 0 of the ring backward: the travelling accumulators start from this rank's contribution -- no memset, no read).
+template <typename T, bool INIT>
+__global__ void __launch_bounds__(256) accum_kernel(float* __restrict__ acc0, const T* __restrict__ part0,
+                                                    float* __restrict__ acc1, const T* __restrict__ part1, size_t n)
 {
+    float* __restrict__ acc = blockIdx.y ? acc1 : acc0;
+    const T* __restrict__ part = blockIdx.y ? part1 : part0;
     size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (i + 3 < n) {
-        float4 a = *reinterpret_cast<float4*>(acc + i);
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (!INIT) a = *reinterpret_cast<float4*>(acc + i);
         float p0, p1, p2, p3;
         if constexpr (sizeof(T) == 4) {
             float4 p = *reinterpret_cast<const float4*>(part + i); p0 = p.x; p1 = p.y; p2 = p.z; p3 = p.w;
@@ -288,7 +293,8 @@ __global__ void __launch_bounds__(256) accum_kernel(float* __restrict__ acc, con
         *reinterpret_cast<float4*>(acc + i) = a;
     } else {
         for (; i < n; ++i) {
-            if constexpr (sizeof(T) == 4) acc[i] += part[i]; else acc[i] += __bfloat162float(part[i]);
+            const float pv = sizeof(T) == 4 ? (float)part[i] : __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(&part[i]));
+            acc[i] = INIT ? pv : acc[i] + pv;
         }
     }
 }
@@ -323,14 +329,25 @@ __global__ void __launch_bounds__(256) cast_kernel(T* __restrict__ out, const fl
         if constexpr (sizeof(T) == 4) out[i] = acc[i]; else out[i] = __float2bfloat16_rn(acc[i]);
     }
 }
-static int accum(float* acc, const void* part, size_t n, int dtype, cudaStream_t st)
+// one launch for up to two (accumulator, partial) pairs of n elements each; acc1 == nullptr: a single pair
+static int accum2(float* acc0, const void* part0, float* acc1, const void* part1, size_t n, int dtype, bool init, cudaStream_t st)
 {
-    unsigned grid = (unsigned)((n / 4 + 255) / 256 + 1);
-    if (dtype == B200_DTYPE_F32) accum_kernel<float><<<grid, 256, 0, st>>>(acc, (const float*)part, n);
-    else accum_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(acc, (const __nv_bfloat16*)part, n);
+    if (n == 0) return B200_OK;
+    dim3 grid((unsigned)((n / 4 + 255) / 256 + 1), acc1 ? 2 : 1);
+    if (dtype == B200_DTYPE_F32) {
+        if (init) accum_kernel<float, true><<<grid, 256, 0, st>>>(acc0, (const float*)part0, acc1, (const float*)part1, n);
+        else accum_kernel<float, false><<<grid, 256, 0, st>>>(acc0, (const float*)part0, acc1, (const float*)part1, n);
+    } else {
+        if (init) accum_kernel<__nv_bfloat16, true><<<grid, 256, 0, st>>>(acc0, (const __nv_bfloat16*)part0, acc1, (const __nv_bfloat16*)part1, n);
+        else accum_kernel<__nv_bfloat16, false><<<grid, 256, 0, st>>>(acc0, (const __nv_bfloat16*)part0, acc1, (const __nv_bfloat16*)part1, n);
+    }
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
+}
+static int accum(float* acc, const void* part, size_t n, int dtype, cudaStream_t st)
+{
+    return accum2(acc, part, nullptr, nullptr, n, dtype, false, st);
 }
 static int accum_rows(float* acc, const void* part, size_t slabs, int slab_rows, int nrows, int d, int dtype, cudaStream_t st)
 {
@@ -479,7 +496,13 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     // on copy-engine traffic that is independent of every SM.
     {
         const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
-        const bool want = g_fwd_mode != 1 && !causal && (long long)B * H <= 65535 && (al & 15) == 0 &&
+        // AUTO: a CTA of the persistent kernel needs block s+1 one CTA-block-time after block s (~4 * 256 * Nl * d FLOP on one
+        // SM), while the stepwise schedule only needs it a whole launch later -- so persistent pays when a block's transfer
+        // (2 * BH * Nl * d elements over NVLink) fits into that time, i.e. for few heads per rank (C4 at 8 GPUs: 0.10 ms
+        // against 0.13 ms), and stalls its first waves otherwise (measured at 2 GPUs, BH = 64: 4.12 against 3.59 ms).
+        const double t_xfer = 2.0 * B * H * Nl * d * 2.0 / 650e9, t_cta_block = 4.0 * 256.0 * Nl * d / (1250e12 / num_sms());
+        const bool pays = g_fwd_mode == 2 || t_xfer <= 0.9 * t_cta_block;
+        const bool want = g_fwd_mode != 1 && pays && !causal && (long long)B * H <= 65535 && (al & 15) == 0 &&
                           fwd_ring_persistent_supported(dtype, d, B * H, Nl, nranks) && nranks <= 256;
         if (want) {
             const size_t need = 2 * (size_t)(nranks - 1) * kv_bytes;      // (kv_bytes is a multiple of 16 KB here)
@@ -725,8 +748,11 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
         B200_TRY(tc_bwd_ring_prepare(L, Dvec, stats, B * H, Nl, st));
     }
     B200_CUDA_TRY(cudaMemsetAsync(dQa, 0, acc_bytes, st));
-    B200_CUDA_TRY(cudaMemsetAsync(dKa[0], 0, acc_bytes, st));
-    B200_CUDA_TRY(cudaMemsetAsync(dVa[0], 0, acc_bytes, st));
+    // (dKa[0] / dVa[0] are written, not accumulated into, by step 0: no memset)
+    const int BH = B * H;
+    const int Nl_pad64 = (Nl + 63) / 64 * 64;
+    const float* L2p = reinterpret_cast<const float*>(stats);
+    const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + align256((size_t)BH * Nl_pad64 * sizeof(float)));
     B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
     B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
     if (ce) B200_TRY(call_begin(lk, rs));
@@ -758,47 +784,64 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
         }
         const int blk = (rank - step + nranks) % nranks;
         const bool first_half_only = causal && step > 0 && blk < rank;   // dK/dV of this step exist for rows [0, c) only
-        if (fused) {
-            const float sc = scale == 0.0f ? 1.0f / sqrtf((float)d) : scale;
-            if (!causal) B200_TRY(tc_bwd_ring_step(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, Nl, sc, st));
-            else if (step == 0) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, Nl, true, sc, st));
-            else if (blk < rank) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, c, false, sc, st));
-            else B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, c, c, Nl, false, sc, st));
-        } else {
-            B200_TRY(b200_fa2_bwd(Q, Kc, Vc, O, L, dO, dQp, dKp, dVp, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st));
-            B200_TRY(accum(dQa, dQp, n_el, dtype, st));
+        // The LAST step is cut into head groups: a group's accumulators start their final hop (home) while the next group
+        // computes, so only the last group's transfer is exposed (r1: the whole 2 x acc_bytes hop was -- 0.75 ms of an
+        // 11.9 ms call at 2 GPUs).  Groups keep >= ~6 waves of CTAs each, so small per-rank head counts are not split.
+        int groups = 1;
+        if (fused && !causal && step == nranks - 1) {
+            const long long ctas = (long long)BH * ((Nl + 127) / 128);
+            groups = (int)std::max<long long>(1, std::min<long long>(std::min(4, BH), ctas / (6 * num_sms())));
         }
-        // the running dK/dV of this block arrive from the previous rank while we compute
-        if (step >= 1) {
-            if (ce) B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
-            else B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
-        }
-        if (first_half_only) {
-            B200_TRY(accum_rows(dKa[cur], dKp, (size_t)B * H, Nl, c, d, dtype, st));
-            B200_TRY(accum_rows(dVa[cur], dVp, (size_t)B * H, Nl, c, d, dtype, st));
-        } else {
-            B200_TRY(accum(dKa[cur], dKp, n_el, dtype, st));
-            B200_TRY(accum(dVa[cur], dVp, n_el, dtype, st));
-        }
-        // hand the accumulators to the next rank (queued behind this step's K/V prefetch)
-        B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
-        B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
-        if (ce) {
-            const int dst = cur ^ 1;
-            // the neighbour's accumulator pair `dst` must have been passed on as often as ours was
-            if (lk.out_acc[dst] > 0) B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_FREE_ACC + dst, lk.out_acc[dst]));
-            B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dKa[dst]), dKa[cur], acc_bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
-            B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dVa[dst]), dVa[cur], acc_bytes, cudaMemcpyDeviceToDevice, rs->comm_stream));
-            B200_TRY(write_val(rs->comm_stream, lk.next_flags + F_RDY_ACC + dst, ++lk.push_acc[dst]));
-            B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_ACC + cur, ++lk.out_acc[cur]));
-            if (step >= 1)      // this step's K/V block (compute + onward push both ordered before this point) is released too
-                B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
-        } else {
-            const void* s[2] = {dKa[cur], dVa[cur]};
-            void* r[2] = {dKa[cur ^ 1], dVa[cur ^ 1]};
-            size_t b[2] = {acc_bytes, acc_bytes};
-            B200_TRY(exchange(s, r, b, 2, next, prev, comm, rs->comm_stream));
-            B200_CUDA_TRY(cudaEventRecord(rs->ev_acc, rs->comm_stream));
+        const size_t es_part = dtype == B200_DTYPE_F32 ? 4 : 2;
+        for (int g = 0; g < groups; ++g) {
+            const int h0 = (int)((long long)BH * g / groups), h1 = (int)((long long)BH * (g + 1) / groups);
+            const size_t e0 = (size_t)h0 * Nl * d, ne = (size_t)(h1 - h0) * Nl * d;     // element range of this head group
+            if (fused) {
+                const float sc = scale == 0.0f ? 1.0f / sqrtf((float)d) : scale;
+                if (!causal) B200_TRY(tc_bwd_ring_step_heads(Q, Kc, Vc, dO, L2p, Dp, dQa, dKp, dVp, h0, h1 - h0, Nl, 0, Nl, Nl, false, sc, st));
+                else if (step == 0) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, Nl, true, sc, st));
+                else if (blk < rank) B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, 0, Nl, c, false, sc, st));
+                else B200_TRY(tc_bwd_ring_step_sub(Q, Kc, Vc, dO, stats, dQa, dKp, dVp, B * H, Nl, c, c, Nl, false, sc, st));
+            } else {
+                B200_TRY(b200_fa2_bwd(Q, Kc, Vc, O, L, dO, dQp, dKp, dVp, B, H, Nl, Nl, d, scale, dtype, nullptr, 0, st));
+                B200_TRY(accum(dQa, dQp, n_el, dtype, st));
+            }
+            // the running dK/dV of this block arrive from the previous rank while we compute
+            if (step >= 1 && g == 0) {
+                if (ce) B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
+                else B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
+            }
+            if (first_half_only) {
+                B200_TRY(accum_rows(dKa[cur], dKp, (size_t)B * H, Nl, c, d, dtype, st));
+                B200_TRY(accum_rows(dVa[cur], dVp, (size_t)B * H, Nl, c, d, dtype, st));
+            } else {
+                // (step 0: the accumulators START as this rank's contribution -- written, not added to a zeroed buffer)
+                B200_TRY(accum2(dKa[cur] + e0, (const uint8_t*)dKp + e0 * es_part, dVa[cur] + e0, (const uint8_t*)dVp + e0 * es_part, ne, dtype,
+                                step == 0, st));
+            }
+            // hand the accumulators to the next rank (queued behind this step's K/V prefetch)
+            B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
+            B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+            const bool last_group = g == groups - 1;
+            if (ce) {
+                const int dst = cur ^ 1;
+                // the neighbour's accumulator pair `dst` must have been passed on as often as ours was
+                if (g == 0 && lk.out_acc[dst] > 0) B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_FREE_ACC + dst, lk.out_acc[dst]));
+                B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dKa[dst] + e0), dKa[cur] + e0, ne * sizeof(float), cudaMemcpyDeviceToDevice, rs->comm_stream));
+                B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + off(dVa[dst] + e0), dVa[cur] + e0, ne * sizeof(float), cudaMemcpyDeviceToDevice, rs->comm_stream));
+                if (last_group) {
+                    B200_TRY(write_val(rs->comm_stream, lk.next_flags + F_RDY_ACC + dst, ++lk.push_acc[dst]));
+                    B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_ACC + cur, ++lk.out_acc[cur]));
+                    if (step >= 1)      // this step's K/V block (compute + onward push both ordered before this point) is released too
+                        B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
+                }
+            } else {
+                const void* sx[2] = {dKa[cur] + e0, dVa[cur] + e0};
+                void* rx[2] = {dKa[cur ^ 1] + e0, dVa[cur ^ 1] + e0};
+                size_t bx[2] = {ne * sizeof(float), ne * sizeof(float)};
+                B200_TRY(exchange(sx, rx, bx, 2, next, prev, comm, rs->comm_stream));
+                if (last_group) B200_CUDA_TRY(cudaEventRecord(rs->ev_acc, rs->comm_stream));
+            }
         }
         cur ^= 1;
         if (!ce && step < nranks - 1) {
@@ -807,6 +850,8 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
         }
         if (step < nranks - 1) { Kc = Kb[slot]; Vc = Vb[slot]; }
     }
+    // dQ never travelled: its cast runs under the accumulators' last hop
+    B200_TRY(cast_out(dQ, dQa, n_el, dtype, st));
     // after P hops the accumulators of block `rank` are back home (in pair `cur`)
     if (ce) {
         B200_TRY(wait_ge(st, lk.flags + F_RDY_ACC + cur, ++lk.in_acc[cur]));
@@ -815,7 +860,6 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
     } else {
         B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_acc, 0));
     }
-    B200_TRY(cast_out(dQ, dQa, n_el, dtype, st));
     B200_TRY(cast_out(dK, dKa[cur], n_el, dtype, st));
     B200_TRY(cast_out(dV, dVa[cur], n_el, dtype, st));
     if (ce) B200_TRY(call_end(lk, rs, st));          // (behind the casts: the home accumulators have been read)

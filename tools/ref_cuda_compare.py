@@ -37,6 +37,20 @@ def timed(fn, reps, warm=3):
     return e0.elapsed_time(e1) / reps
 
 
+def timed_host(fn, reps, warm=1):
+    """Wall clock around a synchronised loop: for the reference wrappers, which launch on the legacy default stream of
+    their own module (CUDA events recorded through torch did not bracket those launches reliably: r2b log)."""
+    import time
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) * 1e3 / reps
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=4096)
@@ -52,8 +66,6 @@ def main():
     mk = lambda s: (torch.rand(1, H, N, d, device="cuda", generator=g) - 0.5) * 2 * s
     Q, K, V, dO = mk(0.5), mk(0.5), mk(0.5), mk(0.2)
     out = {"config": f"C2-shaped: B=1 H={H} N={N} d={d} fp32 I/O, scale 1/sqrt(d), uniform(-0.5,0.5) inputs", "reps": a.reps}
-    cur = torch.cuda.current_stream()
-    legacy = torch.cuda.ExternalStream(0)          # the reference wrappers launch on the legacy default stream
 
     # ---------------- forward
     O_ref, L_ref = torch.empty_like(Q), torch.empty(1, H, N, device="cuda")
@@ -61,8 +73,8 @@ def main():
         for h in range(H):
             rc = oracle.ref_cuda_forward(Q[0, h], K[0, h], V[0, h], O_ref[0, h], L_ref[0, h], sc)
             assert rc == 0, rc
-    with torch.cuda.stream(legacy):
-        t_ref_f = timed(ref_fwd, max(2, a.reps // 4))
+    t_ref_f = timed_host(ref_fwd, max(2, a.reps // 4))
+    t_ref_f_events = timed(ref_fwd, 2, warm=0)
     O, L = fa.flash_attention_2_forward(Q, K, V, sc)
     t_our_f = timed(lambda: fa.flash_attention_2_forward(Q, K, V, sc), a.reps)
     def ours_per_head():
@@ -77,7 +89,7 @@ def main():
     Oo, Lo = oracle.forward_rows(Q[0, h0].cpu().numpy(), K[0, h0].cpu().numpy(), V[0, h0].cpu().numpy(), rows, sc)
     flops_f = 4.0 * H * N * N * d
     out["forward"] = {
-        "reference_cuda_ms": t_ref_f, "ours_batched_tf32_ms": t_our_f, "ours_per_head_calls_tf32_ms": t_our_f1, "ours_batched_bf16_ms": t_our_fb,
+        "reference_cuda_ms": t_ref_f, "reference_cuda_ms_by_events": t_ref_f_events, "ours_batched_tf32_ms": t_our_f, "ours_per_head_calls_tf32_ms": t_our_f1, "ours_batched_bf16_ms": t_our_fb,
         "reference_cuda_tflops": flops_f / t_ref_f / 1e9, "ours_tf32_tflops": flops_f / t_our_f / 1e9, "ours_bf16_tflops": flops_f / t_our_fb / 1e9,
         "speedup_tf32_vs_reference_cuda": t_ref_f / t_our_f,
         "max_abs_O_ours_vs_reference_cuda": float((O - O_ref).abs().max()), "max_abs_L_ours_vs_reference_cuda": float((L - L_ref).abs().max()),
@@ -93,8 +105,7 @@ def main():
             rc = oracle.ref_cuda_backward(Q[0, h], K[0, h], V[0, h], O_ref[0, h], L_ref[0, h], dO[0, h],
                                           g_ref[0][0, h], g_ref[1][0, h], g_ref[2][0, h], sc)
             assert rc == 0, rc
-    with torch.cuda.stream(legacy):
-        t_ref_b = timed(ref_bwd, max(2, a.reps // 4), warm=1)
+    t_ref_b = timed_host(ref_bwd, max(2, a.reps // 4))
     ours = fa.flash_attention_2_backward(Q, K, V, O, L, dO, sc)
     t_our_b = timed(lambda: fa.flash_attention_2_backward(Q, K, V, O, L, dO, sc), a.reps)
     dob = dO.bfloat16()
