@@ -76,7 +76,9 @@ static bool bwd_routes_tc(const void* Q, const void* K, const void* V, const voi
                           const void* dV, int dtype, int d, int Nq, int Nkv, bool causal)
 {
     const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
-    return !g_force_generic && tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv) && (al & 15) == 0;
+    if (g_force_generic || (al & 15) != 0) return false;
+    if (tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) return !causal;            // fp32 I/O: tf32 kernel, non-causal only
+    return tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv);
 }
 
 static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
@@ -100,6 +102,7 @@ static size_t bwd_ws_bytes(int BH, int Nq, int Nkv, int d, int dtype)
 {
     size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
     size_t tc = tc_bwd_supported(dtype, d, Nq, Nkv) ? tc_bwd_workspace_bytes(BH, Nq, Nkv, d, dtype) : 0;
+    if (tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) tc = tc_bwd_tf32_workspace_bytes(BH, Nq, Nkv);
     return dbytes + tc;
 }
 
@@ -121,9 +124,12 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     float* D = reinterpret_cast<float*>(ws);
     const size_t dbytes = (((size_t)BH * Nq * sizeof(float)) + 255) & ~(size_t)255;
     B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
-    if (bwd_routes_tc(Q, K, V, dO, dQ, dK, dV, dtype, d, Nq, Nkv, causal))
+    if (bwd_routes_tc(Q, K, V, dO, dQ, dK, dV, dtype, d, Nq, Nkv, causal)) {
+        if (dtype == B200_DTYPE_F32)
+            return tc_bwd_tf32(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, scale, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
         return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
                       reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st, causal);
+    }
     return simt_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
 }
 
@@ -259,7 +265,8 @@ __attribute__((visibility("default"))) int b200_debug_trace_read_bwd(long long* 
 int b200_debug_force_generic(int on) { int old = g_force_generic; g_force_generic = on ? 1 : 0; return old; }
 
 int b200_fwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_fwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
-int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv) { return tc_bwd_supported(dtype, d, Nq, Nkv) ? 1 : 0; }
+int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv)
+{ return (tc_bwd_supported(dtype, d, Nq, Nkv) || tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) ? 1 : 0; }
 
 int b200_fa2_fwd_route(const void* Q, const void* K, const void* V, const void* O, int Nq, int Nkv, int d, float scale,
                        int dtype, int flags)

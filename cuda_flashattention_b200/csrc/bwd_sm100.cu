@@ -493,6 +493,17 @@ pad_stats_kernel(const float* __restrict__ L, const float* __restrict__ D, float
     else { L2p[idx] = INFINITY; Dp[idx] = 0.0f; }
 }
 
+// (also used by the tf32 backward, bwd_tf32_sm100.cu)
+int pad_stats(const float* L, const float* D, float* L2p, float* Dp, int BH, int Nq, cudaStream_t st)
+{
+    const int Nq_pad = (Nq + 63) / 64 * 64;
+    const size_t total = (size_t)BH * Nq_pad;
+    pad_stats_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(L, D, L2p, Dp, Nq, Nq_pad, total, Nq);
+    B200_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return B200_OK;
+}
+
 __global__ void __launch_bounds__(256)
 cast_dq_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ out, size_t n4)
 {
