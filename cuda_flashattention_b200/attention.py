@@ -231,27 +231,54 @@ def attention_backward(q, k, v, O, L, dO, causal=False, softmax_scale=None, layo
     return dQ, dK, dV
 
 
-class _FlashAttnFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, q, k, v, causal, softmax_scale, layout):
-        O, L = attention_forward(q, k, v, causal, softmax_scale, layout)
-        ctx.save_for_backward(q, k, v, O, L)
-        ctx.cfg = (causal, softmax_scale, layout)
-        return O
+# Registered operators ("a torch.library custom-op binding so the kernels are usable from a model"): opaque to
+# torch.compile / AOT autograd (fake implementations give shapes and strides, the backward is its own op), so a model
+# that calls flash_attn_func traces as ONE node per direction instead of graph-breaking on ctypes.
+@torch.library.custom_op("b200attn::fwd", mutates_args=(), device_types="cuda")
+def _op_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool, softmax_scale: float, layout: str) -> tuple[torch.Tensor, torch.Tensor]:
+    return attention_forward(q, k, v, causal, softmax_scale, layout)
 
-    @staticmethod
-    def backward(ctx, dO):
-        q, k, v, O, L = ctx.saved_tensors
-        causal, softmax_scale, layout = ctx.cfg
-        dQ, dK, dV = attention_backward(q, k, v, O, L, dO, causal, softmax_scale, layout)
-        return dQ, dK, dV, None, None, None
+
+@_op_fwd.register_fake
+def _(q, k, v, causal, softmax_scale, layout):
+    B, H, Nq = (q.shape[0], q.shape[1], q.shape[2]) if layout == "bhnd" else (q.shape[0], q.shape[2], q.shape[1])
+    return torch.empty_like(q, memory_format=torch.contiguous_format), q.new_empty((B, H, Nq), dtype=torch.float32)
+
+
+@torch.library.custom_op("b200attn::bwd", mutates_args=(), device_types="cuda")
+def _op_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, O: torch.Tensor, L: torch.Tensor, dO: torch.Tensor, causal: bool,
+            softmax_scale: float, layout: str) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    return attention_backward(q, k, v, O, L, dO, causal, softmax_scale, layout)
+
+
+@_op_bwd.register_fake
+def _(q, k, v, O, L, dO, causal, softmax_scale, layout):
+    return (torch.empty_like(q, memory_format=torch.contiguous_format), torch.empty_like(k, memory_format=torch.contiguous_format),
+            torch.empty_like(v, memory_format=torch.contiguous_format))
+
+
+def _op_setup(ctx, inputs, output):
+    q, k, v, causal, softmax_scale, layout = inputs
+    O, L = output
+    ctx.save_for_backward(q, k, v, O, L)
+    ctx.cfg = (causal, softmax_scale, layout)
+
+
+def _op_backward(ctx, dO, dL):
+    q, k, v, O, L = ctx.saved_tensors
+    causal, softmax_scale, layout = ctx.cfg
+    dQ, dK, dV = _op_bwd(q, k, v, O, L, dO.contiguous(), causal, softmax_scale, layout)
+    return dQ, dK, dV, None, None, None
+
+
+_op_fwd.register_autograd(_op_backward, setup_context=_op_setup)
 
 
 def flash_attn_func(q, k, v, causal=False, softmax_scale=None, layout="bnhd"):
     """Differentiable exact attention on the tcgen05 kernels.  q [B,Nq,H,d], k/v [B,Nkv,Hkv,d] (layout='bnhd', the
     token-major order models use) or [B,H,N,d] (layout='bhnd'); any batch/head/row strides with a contiguous last
     dimension (e.g. slices of a packed qkv projection); Hkv may divide H (GQA / MQA)."""
-    return _FlashAttnFn.apply(q, k, v, causal, softmax_scale, layout)
+    return _op_fwd(q, k, v, bool(causal), float(softmax_scale or 0.0), layout)[0]
 
 
 # ---- packed variable-length batches (b200_fa2_fwd_varlen / b200_fa2_bwd_varlen) ----------------------

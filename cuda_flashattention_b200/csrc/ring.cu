@@ -496,12 +496,18 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     // on copy-engine traffic that is independent of every SM.
     {
         const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
-        // AUTO: a CTA of the persistent kernel needs block s+1 one CTA-block-time after block s (~4 * 256 * Nl * d FLOP on one
-        // SM), while the stepwise schedule only needs it a whole launch later -- so persistent pays when a block's transfer
-        // (2 * BH * Nl * d elements over NVLink) fits into that time, i.e. for few heads per rank (C4 at 8 GPUs: 0.10 ms
-        // against 0.13 ms), and stalls its first waves otherwise (measured at 2 GPUs, BH = 64: 4.12 against 3.59 ms).
+        // AUTO picks the persistent schedule only for single-wave problems (all CTAs of the call resident at once) whose
+        // per-block transfer (2 * BH * Nl * d elements over NVLink) fits a CTA's per-block compute time (~4 * 256 * Nl * d FLOP
+        // on one SM).  A CTA of the persistent kernel needs block s+1 one CTA-block-time after block s, the stepwise
+        // schedule only a whole launch later, so with several waves of CTAs the first wave stalls on the hop chain while
+        // holding every SM: measured at C4's shape, 512 CTAs per rank, 8 GPUs: 4.19 ms against 3.56 ms stepwise (and
+        // 7.2 ms inside the fwd+bwd loop, where the ranks enter the call skewed); 2 GPUs, 2048 CTAs: 3.96 against 3.70 ms
+        // (profiles/r2c_bench_8gpu_persistent_auto.json, r2b_bench_2gpu.json).  b200_ring_set_forward_mode(2) forces it.
         const double t_xfer = 2.0 * B * H * Nl * d * 2.0 / 650e9, t_cta_block = 4.0 * 256.0 * Nl * d / (1250e12 / num_sms());
-        const bool pays = g_fwd_mode == 2 || t_xfer <= 0.9 * t_cta_block;
+        const long long n_ctas = (long long)B * H * ((Nl + 255) / 256);
+        // (2 GPUs, tools/ring_modes.py, profiles/r2c_ring_modes_2gpu.txt: 128-256 CTAs per rank +0.5 ... +3.8 %, 64 CTAs -36 %
+        // -- the stepwise schedule runs two half-empty steps side by side on its two streams -- 512 CTAs -3.5 %)
+        const bool pays = g_fwd_mode == 2 || (n_ctas <= num_sms() && 2 * n_ctas > num_sms() && t_xfer <= 0.9 * t_cta_block);
         const bool want = g_fwd_mode != 1 && pays && !causal && (long long)B * H <= 65535 && (al & 15) == 0 &&
                           fwd_ring_persistent_supported(dtype, d, B * H, Nl, nranks) && nranks <= 256;
         if (want) {
@@ -529,10 +535,10 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
                     B200_CUDA_TRY(cudaMemcpyAsync(lk.next_buf + (size_t)(nranks - 1 + s) * kv_bytes, vs, kv_bytes, cudaMemcpyDeviceToDevice,
                                                   rs->comm_stream));
                     B200_TRY(write_val(rs->comm_stream, lk.next_flags + F_PRDY + s + 1, epoch));
+                    // the caller may reuse K/V (the source of the FIRST push only) once its stream has passed this call
+                    if (s == 0) B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
                 }
                 B200_TRY(launch_fwd_ring_persistent(Q, K, V, O, L, Ks, Vs, lk.flags + F_PRDY, epoch, B * H, Nl, nranks, sc, st));
-                // the caller may reuse K/V (the source of the first push) once its stream has passed this call
-                B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
                 B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
                 B200_TRY(call_end(lk, rs, st));
                 return B200_OK;

@@ -141,6 +141,24 @@ def test_autograd_expanded_gradient_is_not_read_as_contiguous():
     assert ei.value.status == -8
 
 
+def test_registered_op_traces_under_torch_compile():
+    """flash_attn_func is a torch.library custom op (b200attn::fwd / b200attn::bwd): it has to pass the operator checks and
+    trace without graph breaks (fullgraph=True), forward and backward, with the same numbers as the eager call."""
+    B, N, H, d = 1, 256, 2, 128
+    q, k, v = _rand((B, N, H, d), 21), _rand((B, N, H, d), 22), _rand((B, N, H, d), 23)
+    torch.library.opcheck(torch.ops.b200attn.fwd.default, (q, k, v, True, 0.0, "bnhd"), test_utils=("test_schema", "test_faketensor"))
+
+    def f(q_, k_, v_):
+        return (fa.flash_attn_func(q_ * 1.0, k_, v_, causal=True).float() ** 2).sum()
+
+    qa, ka, va = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    f(qa, ka, va).backward()
+    qc, kc, vc = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    torch.compile(f, backend="aot_eager", fullgraph=True)(qc, kc, vc).backward()
+    for a, b in ((qa.grad, qc.grad), (ka.grad, kc.grad), (va.grad, vc.grad)):
+        assert torch.equal(a, b)
+
+
 @pytest.mark.parametrize("causal,Hkv", [(False, 2), (True, 4), (False, 1)])
 def test_packed_variable_length_batch(causal, Hkv):
     # three sequences of different lengths in one packed [total, H, d] batch (cross lengths when not causal)
