@@ -496,18 +496,15 @@ static int ring_fwd_impl(const void* Q, const void* K, const void* V, void* O, f
     // on copy-engine traffic that is independent of every SM.
     {
         const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
-        // AUTO picks the persistent schedule only for single-wave problems (all CTAs of the call resident at once) whose
-        // per-block transfer (2 * BH * Nl * d elements over NVLink) fits a CTA's per-block compute time (~4 * 256 * Nl * d FLOP
-        // on one SM).  A CTA of the persistent kernel needs block s+1 one CTA-block-time after block s, the stepwise
-        // schedule only a whole launch later, so with several waves of CTAs the first wave stalls on the hop chain while
-        // holding every SM: measured at C4's shape, 512 CTAs per rank, 8 GPUs: 4.19 ms against 3.56 ms stepwise (and
-        // 7.2 ms inside the fwd+bwd loop, where the ranks enter the call skewed); 2 GPUs, 2048 CTAs: 3.96 against 3.70 ms
-        // (profiles/r2c_bench_8gpu_persistent_auto.json, r2b_bench_2gpu.json).  b200_ring_set_forward_mode(2) forces it.
-        const double t_xfer = 2.0 * B * H * Nl * d * 2.0 / 650e9, t_cta_block = 4.0 * 256.0 * Nl * d / (1250e12 / num_sms());
-        const long long n_ctas = (long long)B * H * ((Nl + 255) / 256);
-        // (2 GPUs, tools/ring_modes.py, profiles/r2c_ring_modes_2gpu.txt: 128-256 CTAs per rank +0.5 ... +3.8 %, 64 CTAs -36 %
-        // -- the stepwise schedule runs two half-empty steps side by side on its two streams -- 512 CTAs -3.5 %)
-        const bool pays = g_fwd_mode == 2 || (n_ctas <= num_sms() && 2 * n_ctas > num_sms() && t_xfer <= 0.9 * t_cta_block);
+        // AUTO = stepwise.  The persistent schedule is built, correct (RING_OK at 2 / 4 / 8 ranks) and measured -- and does not
+        // pay on this machine: a CTA of the persistent kernel needs block s+1 one CTA-block-time (~0.12 ms at Nl = 8192) after
+        // block s, the stepwise schedule only a whole launch later, so the first wave stalls on the hop chain (P - 1 sequential
+        // hops of transfer + two stream mem-ops) while holding every SM, and the wave quantisation that costs the stepwise
+        // schedule its efficiency (512 CTAs on 148 SMs) is the same for a persistent launch of the same CTAs.
+        // tools/ring_modes.py: 2 GPUs x0.64 ... x1.04 (profiles/r2c_ring_modes_2gpu.txt), 8 GPUs x0.86 ... x0.98 at 128-512
+        // CTAs per rank (profiles/r2d_ring_modes_8gpu.txt); C4's shape in the fwd+bwd loop 7.2 ms against 4.2 ms.
+        // b200_ring_set_forward_mode(B200_RING_FWD_PERSISTENT) selects it.
+        const bool pays = g_fwd_mode == 2;
         const bool want = g_fwd_mode != 1 && pays && !causal && (long long)B * H <= 65535 && (al & 15) == 0 &&
                           fwd_ring_persistent_supported(dtype, d, B * H, Nl, nranks) && nranks <= 256;
         if (want) {

@@ -280,15 +280,15 @@ B200_API int b200_ring_exchange_kv(const void* send_k, void* recv_k, const void*
 B200_API int b200_ring_set_transport(int mode);
 
 /* Schedule of the ring FORWARD:
- *   B200_RING_FWD_AUTO (0, default)  : PERSISTENT when the shape allows it (bf16, d = 128, N_local a multiple of 64,
- *       non-causal, copy-engine transport usable), else STEPWISE;
+ *   B200_RING_FWD_AUTO (0, default)  : STEPWISE (the faster one on every shape measured at 2 and 8 GPUs);
  *   B200_RING_FWD_STEPWISE (1)       : one attention launch per ring step into its own partial (O_s, LSE_s), one n-way
  *       log-sum-exp merge at the end -- the reference's schedule (common/ring_attention_kernel.cu:197-226) without its
  *       per-step cudaDeviceSynchronize;
  *   B200_RING_FWD_PERSISTENT (2)     : ONE launch per call.  Every K/V block has its own receive slot, the copy engines
  *       forward the blocks around the ring independently of the compute, and the kernel's TMA producer waits on the
  *       arrival counters they write, carrying (m, l, O) across the blocks in registers / TMEM (device-side
- *       waiting instead of host-sequenced steps; no partial buffers, no merge).
+ *       waiting instead of host-sequenced steps; no partial buffers, no merge).  Needs bf16, d = 128, N_local a multiple
+ *       of 64, non-causal and the copy-engine transport; other calls run STEPWISE.
  * Collective like b200_ring_set_transport. */
 #define B200_RING_FWD_AUTO 0
 #define B200_RING_FWD_STEPWISE 1
