@@ -411,6 +411,25 @@ def run_ours(args):
                         "note": "one launch per ring step + n-way LSE merge vs ONE persistent launch waiting on arrival flags (SURVEY 8f-2); "
                                 "the headline line uses the library default (b200_ring_set_forward_mode(0))"}
         check(lib.b200_ring_set_forward_mode(0), "set_forward_mode")
+        fwd(); barrier()
+
+        def time_bwd(mode, n=5):
+            check(lib.b200_ring_set_backward_mode(mode), "set_backward_mode")
+            bwd(); bwd(); barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(n):
+                bwd()
+            a1.record()
+            barrier()
+            tt = torch.tensor([a0.elapsed_time(a1) / n], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+        tb = [(time_bwd(1), time_bwd(0)) for _ in range(2)]          # interleaved, best of two each (clock drift under the power cap)
+        ring_forward["backward_travelling_ms"] = min(x[0] for x in tb)
+        ring_forward["backward_home_ms"] = min(x[1] for x in tb)
+        ring_forward["backward_note"] = ("fp32 (dK,dV) accumulators travelling with the K/V blocks vs bf16 partials pushed straight to the block's "
+                                         "home rank and summed there (the default, b200_ring_set_backward_mode(0))")
         fwd(); bwd(); barrier()
 
     # ---- parity gate on the outputs of the last timed step (outside every timed region)

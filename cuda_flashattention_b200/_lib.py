@@ -75,6 +75,7 @@ _SIGS = {
     "b200_ring_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp, _i, _i, _vp]),
     "b200_ring_set_transport": (_i, [_i]),
     "b200_ring_set_forward_mode": (_i, [_i]),
+    "b200_ring_set_backward_mode": (_i, [_i]),
     "b200_ring_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _i, _vp, _i, _i, _vp]),
     "b200_ring_unique_id": (_i, [_vp]),
     "b200_ring_comm_init": (_i, [C.POINTER(C.c_void_p), _vp, _i, _i]),

@@ -106,7 +106,10 @@ static bool load_memops()
 }
 
 // F_PRDY + s: persistent forward -- block s of the current call has landed in receive slot s - 1 (value = call epoch)
-enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_CALL_DONE = 8, F_PRDY = 16, F_COUNT = 16 + 256 };
+// F_HOME + s: "home" backward -- the dK/dV partial computed at ring step s + 1 has landed in home slot s (value = call epoch)
+// F_DONE_FROM + r: rank r has finished (read everything of) as many ring calls as the value says
+enum { F_RDY_KV = 0, F_FREE_KV = 2, F_RDY_ACC = 4, F_FREE_ACC = 6, F_PRDY = 16, F_HOME = 16 + 256, F_DONE_FROM = 16 + 512,
+       F_COUNT = 16 + 768, kMaxPeers = 64 };
 
 // transport preference (b200_ring_set_transport): -1 = B200_RING_TRANSPORT decides (default: copy engines), 0 = copy engines,
 // 1 = NCCL send/recv.  Collective like the ring calls themselves: every rank holds the same value.
@@ -114,6 +117,9 @@ static int g_transport_pref = -1;
 // forward schedule (b200_ring_set_forward_mode): 0 = automatic, 1 = one launch per ring step + n-way LSE merge,
 // 2 = one persistent launch that walks all blocks (needs the copy-engine transport; else falls back to 1)
 static int g_fwd_mode = 0;
+// backward schedule (b200_ring_set_backward_mode): 0 = automatic (partials pushed to the block's home rank when the
+// copy-engine transport and the tensor-core step kernel are usable), 1 = travelling fp32 accumulators
+static int g_bwd_mode = 0;
 
 struct PeerLink {
     ncclComm_t comm = nullptr;
@@ -124,7 +130,12 @@ struct PeerLink {
     uint8_t* next_buf = nullptr;            // IPC mapping of the next rank's scratch
     uint32_t* next_flags = nullptr;
     uint32_t* prev_flags = nullptr;
-    void* opened[4] = {nullptr, nullptr, nullptr, nullptr};   // mappings to close
+    // every peer's scratch and counters are mapped (the home backward pushes partial gradients straight to the rank that
+    // owns the block; the call-end handshake tells every peer); next_* / prev_* are aliases into these
+    uint8_t* peer_buf[kMaxPeers] = {};
+    uint32_t* peer_flags[kMaxPeers] = {};
+    bool all_peers = false;                 // nranks <= kMaxPeers: peer_buf / peer_flags are valid for every rank != rank
+    uint32_t bwd_epoch = 0;                 // home backward calls made on this link
     size_t exported = 0;                    // scratch size the neighbours have mapped
     void* exported_ptr = nullptr;           // ... and its address (an NCCL-transport call may have re-allocated it since)
     uint32_t calls_done = 0;                // ring calls finished on this link (F_CALL_DONE handshake)
@@ -143,9 +154,11 @@ struct LinkMsg {                            // what every rank publishes
 
 static void link_close(PeerLink& L)
 {
-    for (int i = 0; i < 4; ++i)
-        if (L.opened[i]) { cudaIpcCloseMemHandle(L.opened[i]); L.opened[i] = nullptr; }
-    L.next_buf = nullptr; L.next_flags = nullptr; L.prev_flags = nullptr;
+    for (int i = 0; i < kMaxPeers; ++i) {
+        if (L.peer_buf[i]) { cudaIpcCloseMemHandle(L.peer_buf[i]); L.peer_buf[i] = nullptr; }
+        if (L.peer_flags[i]) { cudaIpcCloseMemHandle(L.peer_flags[i]); L.peer_flags[i] = nullptr; }
+    }
+    L.next_buf = nullptr; L.next_flags = nullptr; L.prev_flags = nullptr; L.all_peers = false;
     (void)cudaGetLastError();
 }
 
@@ -208,15 +221,23 @@ static int link_prepare(RingState* rs, ncclComm_t comm, int rank, int nranks, si
     const int next = (rank + 1) % nranks, prev = (rank - 1 + nranks) % nranks;
     for (int r = 0; r < nranks; ++r) ok = ok && all[r].ok && all[r].bytes == rs->bytes;
     if (ok) {
-        void* nb = nullptr; void* nf = nullptr; void* pf = nullptr;
-        ok = cudaIpcOpenMemHandle(&nb, all[next].buf, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess &&
-             cudaIpcOpenMemHandle(&nf, all[next].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
-        L.opened[0] = nb; L.opened[1] = nf;
-        if (ok) {
-            if (prev == next) pf = nf;
-            else { ok = cudaIpcOpenMemHandle(&pf, all[prev].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess; L.opened[2] = pf; }
+        // map the neighbours (always) and, for rings of up to kMaxPeers ranks, every other rank as well
+        const bool everyone = nranks <= kMaxPeers;
+        for (int r = 0; r < nranks && ok; ++r) {
+            if (r == rank || !(everyone || r == next || r == prev)) continue;
+            const int slot = everyone ? r : (r == next ? 0 : 1);
+            void* pb = nullptr; void* pf = nullptr;
+            ok = cudaIpcOpenMemHandle(&pb, all[r].buf, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            L.peer_buf[slot] = reinterpret_cast<uint8_t*>(pb);
+            if (ok) ok = cudaIpcOpenMemHandle(&pf, all[r].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            L.peer_flags[slot] = reinterpret_cast<uint32_t*>(pf);
         }
-        L.next_buf = reinterpret_cast<uint8_t*>(nb); L.next_flags = reinterpret_cast<uint32_t*>(nf); L.prev_flags = reinterpret_cast<uint32_t*>(pf);
+        if (ok) {
+            L.next_buf = L.peer_buf[everyone ? next : 0];
+            L.next_flags = L.peer_flags[everyone ? next : 0];
+            L.prev_flags = L.peer_flags[everyone ? prev : (prev == next ? 0 : 1)];
+            L.all_peers = everyone;
+        }
         (void)cudaGetLastError();
     }
     // round 3: the link is used only if EVERY rank managed to map its neighbours
@@ -249,14 +270,27 @@ static inline int write_val(cudaStream_t st, uint32_t* addr, uint32_t v)
 // only rank it writes into -- before its first push (call_begin).
 static int call_begin(PeerLink& L, RingState* rs)
 {
-    if (L.calls_done > 0) B200_TRY(wait_ge(rs->comm_stream, L.flags + F_CALL_DONE, L.calls_done));
+    const int next = (L.rank + 1) % L.nranks;
+    if (L.calls_done > 0) B200_TRY(wait_ge(rs->comm_stream, L.flags + F_DONE_FROM + next, L.calls_done));
+    return B200_OK;
+}
+// ... and before the first write of this call into ANY other rank `peer` (the home backward pushes to every rank)
+static int call_begin_peer(PeerLink& L, RingState* rs, int peer)
+{
+    if (L.calls_done > 0) B200_TRY(wait_ge(rs->comm_stream, L.flags + F_DONE_FROM + peer, L.calls_done));
     return B200_OK;
 }
 static int call_end(PeerLink& L, RingState* rs, cudaStream_t st)
 {
     B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
     B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
-    return write_val(rs->comm_stream, L.prev_flags + F_CALL_DONE, ++L.calls_done);
+    ++L.calls_done;
+    if (L.all_peers) {
+        for (int r = 0; r < L.nranks; ++r)
+            if (r != L.rank) B200_TRY(write_val(rs->comm_stream, L.peer_flags[r] + F_DONE_FROM + L.rank, L.calls_done));
+        return B200_OK;
+    }
+    return write_val(rs->comm_stream, L.prev_flags + F_DONE_FROM + L.rank, L.calls_done);   // only the previous rank writes into us
 }
 
 // push two buffers into the next rank's K/V receive slot
@@ -370,6 +404,155 @@ static int cast_out(void* out, const float* acc, size_t n, int dtype, cudaStream
     return B200_OK;
 }
 
+// out = (T)(own + sum of `nslots` partials `slot_stride` elements apart) for the PAIR of tensors selected by blockIdx.y
+__global__ void __launch_bounds__(256) reduce_partials_kernel(__nv_bfloat16* __restrict__ out0, const __nv_bfloat16* __restrict__ own0,
+                                                              const __nv_bfloat16* __restrict__ slots0, __nv_bfloat16* __restrict__ out1,
+                                                              const __nv_bfloat16* __restrict__ own1, const __nv_bfloat16* __restrict__ slots1,
+                                                              size_t n8, int nslots, size_t slot_stride)
+{
+    __nv_bfloat16* __restrict__ out = blockIdx.y ? out1 : out0;
+    const __nv_bfloat16* __restrict__ own = blockIdx.y ? own1 : own0;
+    const __nv_bfloat16* __restrict__ slots = blockIdx.y ? slots1 : slots0;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n8; i += stride) {
+        float acc[8];
+        auto add = [&](const __nv_bfloat16* src, bool first) {
+            const uint4 raw = reinterpret_cast<const uint4*>(src)[i];
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = __bfloat1622float2(h[k]);
+                acc[2 * k] = first ? f.x : acc[2 * k] + f.x;
+                acc[2 * k + 1] = first ? f.y : acc[2 * k + 1] + f.y;
+            }
+        };
+        add(own, true);
+        for (int s = 0; s < nslots; ++s) add(slots + (size_t)s * slot_stride, false);
+        uint4 o;
+        __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) oh[k] = __floats2bfloat162_rn(acc[2 * k], acc[2 * k + 1]);
+        reinterpret_cast<uint4*>(out)[i] = o;
+    }
+}
+
+}  // namespace b200
+using namespace b200;
+
+// "Home" ring backward (copy-engine transport, bf16 d = 128 tensor-core steps, non-causal): K/V rotate as in the forward,
+// but the gradients do not travel with them.  The step that processes block b writes its bf16 (dK, dV) partial into a
+// rotating pair of local buffers and the copy engine pushes it STRAIGHT TO RANK b -- the block's home -- into the slot
+// of that step; after the last step every rank sums its own partial and the P - 1 that arrived (one pass, fp32 in
+// registers, one rounding) into dK / dV.  Against the travelling fp32 accumulators of ring_bwd_impl this halves the
+// NVLink bytes (bf16 partials instead of fp32 accumulators), removes the per-step accumulate kernels and the serial hop
+// chain, and leaves only the last step's push exposed (cut into head groups like before).
+static int ring_bwd_home(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                         void* dQ, void* dK, void* dV, int B, int H, int Nl, int d, float scale, ncclComm_t comm, int rank, int nranks,
+                         cudaStream_t st, bool* done)
+{
+    *done = false;
+    if (nranks > kMaxPeers) return B200_OK;
+    RingState* rs;
+    B200_TRY(ring_state(&rs));
+    const int BH = B * H, dtype = B200_DTYPE_BF16;
+    const size_t n_el = (size_t)BH * Nl * d, kv_bytes = n_el * 2, acc_bytes = n_el * sizeof(float);
+    const size_t kvb = align256(kv_bytes);
+    const size_t d_bytes = align256((size_t)BH * Nl * sizeof(float));
+    const size_t stats_bytes = tc_bwd_ring_stats_bytes(BH, Nl);
+    // scratch: 2 x (K,V) recv | own partial + 2 rotating partials (dK,dV each) | (P-1) home slots (dK,dV each) | dQ fp32 | D | stats
+    const size_t total = 4 * kvb + 6 * kvb + 2 * (size_t)(nranks - 1) * kvb + align256(acc_bytes) + d_bytes + align256(stats_bytes);
+    void* base;
+    bool ce = false;
+    B200_TRY(link_prepare(rs, comm, rank, nranks, total, &base, &ce));
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    PeerLink& lk = g_link[dev];
+    if (!ce || !lk.all_peers) return B200_OK;                       // (the caller falls back to the travelling accumulators)
+    uint8_t* p = reinterpret_cast<uint8_t*>(base);
+    auto off = [&](const void* q) { return (size_t)(reinterpret_cast<const uint8_t*>(q) - reinterpret_cast<uint8_t*>(base)); };
+    void* Kb[2]; void* Vb[2];
+    Kb[0] = p; p += kvb; Vb[0] = p; p += kvb; Kb[1] = p; p += kvb; Vb[1] = p; p += kvb;
+    uint8_t* dKp[3]; uint8_t* dVp[3];                                // [2] = this rank's own block (step 0), [0/1] rotate
+    for (int i = 0; i < 3; ++i) { dKp[i] = p; p += kvb; dVp[i] = p; p += kvb; }
+    uint8_t* homeK = p; p += (size_t)(nranks - 1) * kvb;
+    uint8_t* homeV = p; p += (size_t)(nranks - 1) * kvb;
+    float* dQa = reinterpret_cast<float*>(p); p += align256(acc_bytes);
+    float* Dvec = reinterpret_cast<float*>(p); p += d_bytes;
+    void* stats = p;
+    const int Nl_pad64 = (Nl + 63) / 64 * 64;
+    const float* L2p = reinterpret_cast<const float*>(stats);
+    const float* Dp = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(stats) + align256((size_t)BH * Nl_pad64 * sizeof(float)));
+    const float sc = scale == 0.0f ? 1.0f / sqrtf((float)d) : scale;
+    const uint32_t epoch = ++lk.bwd_epoch;
+
+    B200_TRY(rowdot(dO, O, Dvec, (size_t)BH * Nl, d, dtype, st));
+    B200_TRY(tc_bwd_ring_prepare(L, Dvec, stats, BH, Nl, st));
+    B200_CUDA_TRY(cudaMemsetAsync(dQa, 0, acc_bytes, st));
+    B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
+    B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+    B200_TRY(call_begin(lk, rs));
+
+    const void* Kc = K; const void* Vc = V;
+    for (int step = 0; step < nranks; ++step) {
+        const int slot = step & 1, cur_slot = slot ^ 1;
+        if (step >= 1) {
+            const uint32_t k = ++lk.in_kv[cur_slot];
+            B200_TRY(wait_ge(st, lk.flags + F_RDY_KV + cur_slot, k));
+            B200_TRY(wait_ge(rs->comm_stream, lk.flags + F_RDY_KV + cur_slot, k));
+        }
+        if (step < nranks - 1) B200_TRY(ce_push_kv(lk, rs, slot, Kc, Vc, off(Kb[slot]), off(Vb[slot]), kv_bytes));
+        const int pb = step == 0 ? 2 : (step & 1);
+        // the push that last read this rotating pair (step - 2) must be over before the kernel overwrites it
+        if (step >= 3) B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_compute[pb], 0));
+        const int home = (rank - step + nranks) % nranks;            // the block of this step lives on rank `home`
+        int groups = 1;
+        if (step == nranks - 1) {
+            const long long ctas = (long long)BH * ((Nl + 127) / 128);
+            groups = (int)std::max<long long>(1, std::min<long long>(std::min(4, BH), ctas / (6 * num_sms())));
+        }
+        for (int g = 0; g < groups; ++g) {
+            const int h0 = (int)((long long)BH * g / groups), h1 = (int)((long long)BH * (g + 1) / groups);
+            const size_t b0 = (size_t)h0 * Nl * d * 2, nb = (size_t)(h1 - h0) * Nl * d * 2;      // byte range of the head group
+            B200_TRY(tc_bwd_ring_step_heads(Q, Kc, Vc, dO, L2p, Dp, dQa, dKp[pb], dVp[pb], h0, h1 - h0, Nl, 0, Nl, Nl, false, sc, st));
+            if (step == 0) continue;
+            B200_CUDA_TRY(cudaEventRecord(rs->ev_main, st));
+            B200_CUDA_TRY(cudaStreamWaitEvent(rs->comm_stream, rs->ev_main, 0));
+            if (g == 0) B200_TRY(call_begin_peer(lk, rs, home));
+            B200_CUDA_TRY(cudaMemcpyAsync(lk.peer_buf[home] + off(homeK) + (size_t)(step - 1) * kvb + b0, dKp[pb] + b0, nb, cudaMemcpyDeviceToDevice, rs->comm_stream));
+            B200_CUDA_TRY(cudaMemcpyAsync(lk.peer_buf[home] + off(homeV) + (size_t)(step - 1) * kvb + b0, dVp[pb] + b0, nb, cudaMemcpyDeviceToDevice, rs->comm_stream));
+            if (g == groups - 1) {
+                B200_TRY(write_val(rs->comm_stream, lk.peer_flags[home] + F_HOME + step - 1, epoch));
+                B200_CUDA_TRY(cudaEventRecord(rs->ev_compute[pb], rs->comm_stream));
+                // this step's K/V block (its compute and onward push are both ordered before this point) goes back to the sender
+                B200_TRY(write_val(rs->comm_stream, lk.prev_flags + F_FREE_KV + cur_slot, ++lk.rel_kv[cur_slot]));
+            }
+        }
+        if (step < nranks - 1) { Kc = Kb[slot]; Vc = Vb[slot]; }
+    }
+    // dQ never left: its cast runs under the last pushes
+    B200_TRY(cast_out(dQ, dQa, n_el, dtype, st));
+    for (int s = 0; s + 1 < nranks; ++s) B200_TRY(wait_ge(st, lk.flags + F_HOME + s, epoch));
+    {
+        const size_t n8 = n_el / 8;                                  // (d = 128: a multiple of 8)
+        dim3 grid((unsigned)std::min<size_t>((n8 + 255) / 256, (size_t)148 * 16), 2);
+        reduce_partials_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<__nv_bfloat16*>(dK), reinterpret_cast<const __nv_bfloat16*>(dKp[2]),
+                                                     reinterpret_cast<const __nv_bfloat16*>(homeK), reinterpret_cast<__nv_bfloat16*>(dV),
+                                                     reinterpret_cast<const __nv_bfloat16*>(dVp[2]), reinterpret_cast<const __nv_bfloat16*>(homeV),
+                                                     n8, nranks - 1, kvb / 2);
+        B200_CUDA_TRY(cudaGetLastError());
+        count_launch();
+    }
+    // the caller may reuse K/V once its stream has passed this call (their last reader is the first K/V push)
+    B200_CUDA_TRY(cudaEventRecord(rs->ev_comm[0], rs->comm_stream));
+    B200_CUDA_TRY(cudaStreamWaitEvent(st, rs->ev_comm[0], 0));
+    B200_TRY(call_end(lk, rs, st));
+    *done = true;
+    return B200_OK;
+}
+
+namespace b200 {
+
 static int exchange(const void* const* send, void* const* recv, const size_t* bytes, int n, int next, int prev,
                     ncclComm_t comm, cudaStream_t st)
 {
@@ -411,6 +594,13 @@ int b200_ring_set_forward_mode(int mode)
 {
     if (mode < 0 || mode > 2) return B200_ERR_INVALID_ARGUMENT;
     g_fwd_mode = mode;
+    return B200_OK;
+}
+
+int b200_ring_set_backward_mode(int mode)
+{
+    if (mode < 0 || mode > 1) return B200_ERR_INVALID_ARGUMENT;
+    g_bwd_mode = mode;
     return B200_OK;
 }
 
@@ -718,6 +908,11 @@ static int ring_bwd_impl(const void* Q, const void* K, const void* V, const void
     // tensor-core steps (bf16, d = 128): D and the padded statistics are computed once per call and each step adds
     // its dQ straight into the fp32 accumulator; otherwise every step is a full b200_fa2_bwd + accumulate
     const bool fused = tc_bwd_ring_supported(dtype, d, B * H, Q, K, V, dO) && b200_bwd_uses_tensor_cores(dtype, d, Nl, Nl);
+    if (fused && !causal && g_bwd_mode != 1) {
+        bool done = false;
+        B200_TRY(ring_bwd_home(Q, K, V, O, L, dO, dQ, dK, dV, B, H, Nl, d, scale, comm, rank, nranks, st, &done));
+        if (done) return B200_OK;
+    }
     const size_t d_bytes = align256((size_t)B * H * Nl * sizeof(float));
     const size_t stats_bytes = fused ? tc_bwd_ring_stats_bytes(B * H, Nl) : 0;
     // scratch: 2 x (K,V) recv, 3 partial grads (I/O dtype), dQ fp32 acc, 2 x (dK,dV) fp32 acc, D, padded stats

@@ -295,6 +295,18 @@ B200_API int b200_ring_set_transport(int mode);
 #define B200_RING_FWD_PERSISTENT 2
 B200_API int b200_ring_set_forward_mode(int mode);
 
+/* Schedule of the ring BACKWARD's gradient reduction:
+ *   B200_RING_BWD_AUTO (0, default)     : HOME when usable (copy-engine transport, bf16 d = 128 tensor-core steps,
+ *       non-causal, <= 64 ranks): the step that processes block b pushes its bf16 (dK, dV) partial straight to rank b,
+ *       which sums its own and the P - 1 received partials in one pass -- no travelling accumulators, no per-step
+ *       accumulate kernels, half the NVLink bytes;
+ *   B200_RING_BWD_TRAVELLING (1)        : fp32 (dK, dV) accumulators hop around the ring one step behind the K/V blocks
+ *       (also what the NCCL transport, fp32 and the causal zigzag ring use).
+ * Collective like b200_ring_set_transport. */
+#define B200_RING_BWD_AUTO 0
+#define B200_RING_BWD_TRAVELLING 1
+B200_API int b200_ring_set_backward_mode(int mode);
+
 /* Frees the library's per-device scratch arena (optional; also released at process exit). */
 B200_API int b200_release_workspace(void);
 

@@ -21,14 +21,18 @@ def main():
     # every data plane / forward schedule the library has (include/b200attn.h: b200_ring_set_transport,
     # b200_ring_set_forward_mode): copy engines + persistent forward (the default), copy engines + one launch per step,
     # NCCL send/recv (the reference's ring_exchange_kv; always stepwise)
-    for (transport, fwd_mode, label) in ((0, 2, "copy-engine/persistent"), (0, 1, "copy-engine/stepwise"), (1, 1, "nccl/stepwise")):
+    for (transport, fwd_mode, bwd_mode, label) in ((0, 2, 0, "copy-engine / persistent forward / home backward"),
+                                                   (0, 1, 1, "copy-engine / stepwise forward / travelling-accumulator backward"),
+                                                   (1, 1, 0, "nccl / stepwise forward / travelling-accumulator backward")):
         check(lib.b200_ring_set_transport(transport), "set_transport")
         check(lib.b200_ring_set_forward_mode(fwd_mode), "set_forward_mode")
+        check(lib.b200_ring_set_backward_mode(bwd_mode), "set_backward_mode")
         if rank == 0:
             print("=== ring configuration:", label)
         ok = battery(rank, world, comm) and ok
     check(lib.b200_ring_set_transport(-1), "set_transport")
     check(lib.b200_ring_set_forward_mode(0), "set_forward_mode")
+    check(lib.b200_ring_set_backward_mode(0), "set_backward_mode")
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     comm.close()
@@ -49,8 +53,9 @@ def battery(rank, world, comm):
         to = lambda a: torch.from_numpy(a[:, :, sl].copy()).cuda().to(dtype).contiguous()
         q, k, v, do = to(Q), to(K), to(V), to(dO)
         k0, v0 = k.clone(), v.clone()
-        O, L = fa.ring_attention_forward(q, k, v, comm, 0.0)
-        dQ, dK, dV = fa.ring_attention_backward(q, k, v, O, L, do, comm, 0.0)
+        for _rep in range(2):                          # twice back to back: the second call runs into the first one's scratch
+            O, L = fa.ring_attention_forward(q, k, v, comm, 0.0)
+            dQ, dK, dV = fa.ring_attention_backward(q, k, v, O, L, do, comm, 0.0)
         torch.cuda.synchronize()
         assert torch.equal(k, k0) and torch.equal(v, v0), "K_local/V_local must not be modified"
         # gather the (rounded) full inputs so the oracle sees exactly what the GPUs saw
