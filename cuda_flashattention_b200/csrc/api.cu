@@ -64,13 +64,14 @@ static inline bool valid_dtype(int dt) { return dt == B200_DTYPE_BF16 || dt == B
 static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sqrtf((float)d) : s; }
 
 // The routing predicates, shared by the calls and by b200_fa2_fwd_route / b200_fa2_bwd_route so that what a caller is
-// told is what runs.  Tensor-core path: supported (dtype, d), causal only on square problems, 16-byte aligned bases
-// (TMA), scale > 0 (the kernels fold scale into the running max).  Everything else: generic CUDA-core kernels.
+// told is what runs.  Tensor-core path: supported (dtype, d), 16-byte aligned bases (TMA), scale > 0 (the forward folds
+// scale into the running max); the fp32 (tf32) backward is d = 64, non-causal.  Everything else: generic CUDA-core kernels.
 static bool fwd_routes_tc(const void* Q, const void* K, const void* V, const void* O, int dtype, int d, int Nq, int Nkv,
                           float scale, bool causal)
 {
     const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
-    return !g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv) && (al & 15) == 0 && scale > 0.0f;
+    (void)causal;                   // (causal runs on the tensor cores for any Nq <= Nkv since r2e)
+    return !g_force_generic && tc_fwd_supported(dtype, d, Nq, Nkv) && (al & 15) == 0 && scale > 0.0f;
 }
 static bool bwd_routes_tc(const void* Q, const void* K, const void* V, const void* dO, const void* dQ, const void* dK,
                           const void* dV, int dtype, int d, int Nq, int Nkv, bool causal)
@@ -78,7 +79,7 @@ static bool bwd_routes_tc(const void* Q, const void* K, const void* V, const voi
     const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
     if (g_force_generic || (al & 15) != 0) return false;
     if (tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) return !causal;            // fp32 I/O: tf32 kernel, non-causal only
-    return tc_bwd_supported(dtype, d, Nq, Nkv) && (!causal || Nq == Nkv);
+    return tc_bwd_supported(dtype, d, Nq, Nkv);
 }
 
 static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
@@ -434,7 +435,7 @@ static int varlen_check(const b200_attn_desc* p, int n, const int* cq, const int
     for (int i = 0; i < n; ++i) {
         const int nq = cq[i + 1] - cq[i], nk = ck[i + 1] - ck[i];
         if (nq < 0 || nk < 0 || ((nq == 0) != (nk == 0))) return B200_ERR_INVALID_ARGUMENT;
-        if ((p->flags & B200_FLAG_CAUSAL) && nq != nk) return B200_ERR_UNSUPPORTED;   // tensor-core causal path is square
+        if ((p->flags & B200_FLAG_CAUSAL) && nq > nk) return B200_ERR_INVALID_ARGUMENT;   // bottom-right aligned mask needs Nq <= Nkv
         if (nq > *max_q) *max_q = nq;
         if (nk > *max_k) *max_k = nk;
     }

@@ -133,7 +133,8 @@ __device__ __forceinline__ void bwd_compute_role(int w, uint32_t tmem, uint8_t* 
             // key kv0 + r is hidden from the queries before it: only the two q tiles on the diagonal are affected
             int qt = ii + i_off;
             if (qt >= n_it) qt -= n_it;
-            const int first_visible = kv0 + r - (qt_min + qt) * BM - 32 * w;   // column (of this warpgroup's 32) of query kv0 + r
+            // (`causal` = 1 + (Nkv - Nq): key kv0 + r is visible to the queries q >= kv0 + r - (Nkv - Nq))
+            const int first_visible = kv0 + r - (causal - 1) - (qt_min + qt) * BM - 32 * w;   // column (of this warpgroup's 32) of the first query that sees the key
             if (first_visible > 0) {
 #pragma unroll
                 for (int c = 0; c < 32; ++c) if (c < first_visible) p[c] = 0.0f;
@@ -342,9 +343,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     // Every CTA of a (b,h) slab walks the q tiles in the same cyclic order but starts at a different
     // one: at any moment the CTAs that run together reduce-add into DIFFERENT dQ tiles, so their
     // fp32 atomics do not queue up on the same L2 lines.
-    // Causal (Nq == Nkv): the q tiles before the diagonal (rows < kv0) see none of this CTA's keys and are skipped;
+    // Causal (bottom-right aligned, Nq <= Nkv): the q tiles before the diagonal (rows < kv0 - (Nkv - Nq)) see none of this CTA's keys and are skipped;
     // low blockIdx.x = most work = scheduled first.
-    const int qt_min = causal ? min(kv0 / BM, n_q - 1) : 0;
+    const int qt_min = causal ? min(max(kv0 - (causal - 1), 0) / BM, n_q - 1) : 0;
     const int n_it = n_q - qt_min;
     const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x) % n_it;
     const int n_tot = G * n_it;
@@ -602,7 +603,7 @@ static int bwd_launch(const BwdLaunch& a, cudaStream_t st)
 #endif
     bwd_kernel<DR><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmdO, a.dQacc, tmdK, tmdV, a.L2p, a.Dp, a.Nq,
                                                 a.stat_stride ? a.stat_stride : Nq_pad, a.dq_rows ? a.dq_rows : a.Nq,
-                                                a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 : 0, a.G, a.BHkv);
+                                                a.scale * 1.4426950408889634f, a.scale, dbg, a.causal ? 1 + (a.Nkv - a.Nq) : 0, a.G, a.BHkv);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
@@ -657,7 +658,7 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
            void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, int d, float scale, int dtype,
            void* ws, size_t ws_bytes, cudaStream_t st, bool causal)
 {
-    if (causal && Nq != Nkv) return B200_ERR_UNSUPPORTED;
+    if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
     if ((align & 15) != 0)
         return simt_bwd(Q, K, V, dO, L, Dvec, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype, st, causal ? Nkv - Nq : kNoCausal);
@@ -670,7 +671,7 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
 int tc_bwd_strided(const BwdArgs& g, void* ws, size_t ws_bytes, cudaStream_t st)
 {
     if (!tc_bwd_supported(g.dtype, g.d, g.Nq, g.Nkv)) return B200_ERR_UNSUPPORTED;
-    if (g.causal && g.Nq != g.Nkv) return B200_ERR_UNSUPPORTED;
+    if (g.causal && g.Nq > g.Nkv) return B200_ERR_INVALID_ARGUMENT;
     if (g.B < 1 || g.H < 1 || g.Hkv < 1 || g.H % g.Hkv != 0 || g.B > 65535 || g.H > 65535) return B200_ERR_INVALID_ARGUMENT;
     const uintptr_t align = (uintptr_t)g.Q | (uintptr_t)g.K | (uintptr_t)g.V | (uintptr_t)g.dO | (uintptr_t)g.dQ | (uintptr_t)g.dK | (uintptr_t)g.dV;
     if ((align & 15) != 0 || (g.ldq.sn & 3) || (g.ldq.sh & 3) || (g.ldq.sb & 3)) return B200_ERR_UNSUPPORTED;

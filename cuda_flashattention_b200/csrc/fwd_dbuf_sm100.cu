@@ -75,8 +75,9 @@ __device__ __forceinline__ void dbuf_softmax_role(int t, uint32_t tmem, uint8_t*
     const uint32_t lane_base = uint32_t(warp_in_wg * 32) << 16;
     const uint32_t tS0 = tmem + 128 * t + lane_base;               // score buffer 0 (buffer 1: + 64 columns)
     const uint32_t tO = tmem + 256 + 128 * t + lane_base;
-    // first key column this row must NOT see: Nkv (ragged last tile), and row + 1 under the causal mask
-    const int col_end = causal ? min(Nkv, q0 + t * 128 + wg_thread + 1) : Nkv;
+    // first key column this row must NOT see: Nkv (ragged last tile), and row + 1 + (Nkv - Nq) under the causal mask
+    // (`causal` carries the bottom-right offset: 0 = no mask, 1 + (Nkv - Nq) otherwise)
+    const int col_end = causal ? min(Nkv, q0 + t * 128 + wg_thread + causal) : Nkv;
     const uint64_t scale2 = f2_pack(scale_log2, scale_log2);
 
     float m = -INFINITY, l = 0.0f;                                 // m in log2 units (already scaled)
@@ -282,7 +283,7 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int q0 = (causal ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * (NT * 128);
     const int ntiles = min(NT, (Nq - q0 + 127) / 128);
     const int nkv_all = (Nkv + BC - 1) / BC;
-    auto nkv_of = [&](int t) { return causal ? min(nkv_all, (q0 + t * 128 + 127) / BC + 1) : nkv_all; };
+    auto nkv_of = [&](int t) { return causal ? min(nkv_all, (q0 + t * 128 + 126 + causal) / BC + 1) : nkv_all; };
     const int nkv = nkv_of(ntiles - 1), nkv_first = nkv_of(0);
 
     if (threadIdx.x == 0) {
@@ -457,7 +458,7 @@ fwd_dbuf_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (t < ntiles) {
             const int nkv_t = nkv_of(t);
             // tiles entirely below the diagonal (and not the ragged last one) need no mask
-            const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + 1) / BC, Nkv / BC)) : nkv_t - 1;
+            const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + causal) / BC, Nkv / BC)) : nkv_t - 1;
             dbuf_softmax_role<POLY>(t, tmem, sQ, &bar_S[2 * t], &bar_Pa[2 * t], &bar_Pb[2 * t], &bar_R[t], &bar_O[t], &tmO, Lout, ldL,
                               Nq, Nkv, nkv_t, n_plain, causal, q0, h, b, bh, scale_log2);
         }
@@ -498,7 +499,7 @@ static int launch_fwd_dbuf_t(const FwdArgs& a, int BH_valid, cudaStream_t st)
         (trc = make_tmap_4d(&tmO, a.O, dt, 2, a.B, a.H, a.Nq, D, a.lo.sb, a.lo.sh, a.lo.sn, 128, 64)))
         return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nq + NT * 128 - 1) / (NT * 128), a.H, a.B);
-    fwd_dbuf_kernel<POLY, PEEL, false><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
+    fwd_dbuf_kernel<POLY, PEEL, false><<<grid, THREADS, SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 + (a.Nkv - a.Nq) : 0,
                                                        a.H / a.Hkv, BH_valid, tmK, tmV, RingWalk{nullptr, 0u, 1, 0});
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();

@@ -99,8 +99,9 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     const uint32_t lane_base = uint32_t(warp_in_wg * 32) << 16;
     const uint32_t tS = tmem + 128 * t + lane_base;                // S_t and (aliased) P_t
     const uint32_t tO = tmem + 256 + 128 * t + lane_base;
-    // first key column this row must NOT see: Nkv (ragged last tile), and row + 1 under the causal mask
-    const int col_end = causal ? min(Nkv, q0 + t * 128 + wg_thread + 1) : Nkv;
+    // first key column this row must NOT see: Nkv (ragged last tile), and row + 1 + (Nkv - Nq) under the causal mask
+    // (`causal` carries the bottom-right offset: 0 = no mask, 1 + (Nkv - Nq) otherwise)
+    const int col_end = causal ? min(Nkv, q0 + t * 128 + wg_thread + causal) : Nkv;
     const uint64_t scale2 = f2_pack(scale_log2, scale_log2);
 
     float m = -INFINITY, l = 0.0f;                                 // m in log2 units (already scaled)
@@ -282,12 +283,12 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     // grid (q blocks, heads of the map, batches of the map); K/V head = h / G (grouped-query attention, G = 1: MHA)
     const int h = blockIdx.y, b = blockIdx.z, bh = b * gridDim.y + h, hk = h / G;
     if (bh >= BH) return;                                          // (a re-split contiguous BH may leave the last batch ragged)
-    // causal (Nq == Nkv): the q blocks near the end of the sequence have the most K/V tiles -- schedule them first
+    // causal (bottom-right aligned, Nq <= Nkv): the q blocks near the end of the sequence have the most K/V tiles -- schedule them first
     const int q0 = (causal ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * (NT * 128);
     const int ntiles = min(NT, (Nq - q0 + 127) / 128);
     const int nkv_all = (Nkv + BC - 1) / BC;
     // K/V tiles that query tile t needs (rows q0 + 128 t .. + 127 see keys 0 .. row), and for the whole CTA
-    auto nkv_of = [&](int t) { return causal ? min(nkv_all, (q0 + t * 128 + 127) / BC + 1) : nkv_all; };
+    auto nkv_of = [&](int t) { return causal ? min(nkv_all, (q0 + t * 128 + 126 + causal) / BC + 1) : nkv_all; };
     const int nkv = nkv_of(ntiles - 1), nkv_first = nkv_of(0);
 
     if (threadIdx.x == 0) {
@@ -468,7 +469,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         if (t < ntiles) {
             const int nkv_t = nkv_of(t);
             // tiles entirely below the diagonal (and not the ragged last one) need no mask
-            const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + 1) / BC, Nkv / BC)) : nkv_t - 1;
+            const int n_plain = causal ? min(nkv_t, min((q0 + t * 128 + causal) / BC, Nkv / BC)) : nkv_t - 1;
             softmax_role<C>(t, tmem, sQ, &bar_S[t], &bar_Pa[t], &bar_Pb[t], &bar_O[t], &tmO, Lout, ldL, Nq, Nkv, nkv_t, n_plain,
                             causal, q0, h, b, bh, scale_log2);
         }
@@ -502,7 +503,7 @@ static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
         (trc = make_tmap_4d(&tmO, a.O, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::CPB)))
         return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nq + C::NT * 128 - 1) / (C::NT * 128), a.H, a.B);
-    fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 : 0,
+    fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 + (a.Nkv - a.Nq) : 0,
                                                      a.H / a.Hkv, BH_valid);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
@@ -569,7 +570,7 @@ static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
 int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int BH, int Nq, int Nkv, int d,
            float scale, int dtype, cudaStream_t st, bool causal)
 {
-    if (causal && Nq != Nkv) return B200_ERR_UNSUPPORTED;
+    if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
     const uintptr_t align = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)O;
     if ((align & 15) != 0 || !(scale > 0.0f))      // TMA needs 16-byte bases; max(S)*scale needs scale > 0
         return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
@@ -584,7 +585,7 @@ int tc_fwd(const void* Q, const void* K, const void* V, void* O, float* L, int B
 int tc_fwd_strided(const FwdArgs& a, cudaStream_t st)
 {
     if (!tc_fwd_supported(a.dtype, a.d, a.Nq, a.Nkv) || !(a.scale > 0.0f)) return B200_ERR_UNSUPPORTED;
-    if (a.causal && a.Nq != a.Nkv) return B200_ERR_UNSUPPORTED;
+    if (a.causal && a.Nq > a.Nkv) return B200_ERR_INVALID_ARGUMENT;
     if (a.B < 1 || a.H < 1 || a.Hkv < 1 || a.H % a.Hkv != 0 || a.B > 65535 || a.H > 65535) return B200_ERR_INVALID_ARGUMENT;
     const uintptr_t align = (uintptr_t)a.Q | (uintptr_t)a.K | (uintptr_t)a.V | (uintptr_t)a.O;
     if ((align & 15) != 0) return B200_ERR_UNSUPPORTED;

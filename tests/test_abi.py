@@ -107,7 +107,7 @@ def test_descriptor_and_varlen_argument_checks_without_device():
     ok_k = (C.c_int * 3)(0, 10, 40)
     assert fa.lib.b200_fa2_fwd_varlen(d, 2, bad, bad, 8, 8, 8, 8, 8, None) == -1
     d.flags = 1
-    assert fa.lib.b200_fa2_fwd_varlen(d, 2, ok, ok_k, 8, 8, 8, 8, 8, None) == -8         # unsupported: causal with Nq != Nkv
+    assert fa.lib.b200_fa2_fwd_varlen(d, 2, ok_k, ok, 8, 8, 8, 8, 8, None) == -1         # causal with a sequence of Nq > Nkv
     assert fa.lib.b200_fa2_fwd_varlen(d, 0, None, None, None, None, None, None, None, None) == 0
     # ring: unknown flags / bad ranks are rejected before anything else
     assert fa.lib.b200_ring_fwd_ex(8, 8, 8, 8, 8, 1, 1, 64, 128, 0.0, 0, 4, None, 0, 2, None) == -1
@@ -116,7 +116,7 @@ def test_descriptor_and_varlen_argument_checks_without_device():
 
 def test_route_query_reports_the_demotions():
     """b200_fa2_fwd_route / b200_fa2_bwd_route tell a caller which kernel family ONE call runs on, including the demotions
-    b200_*_uses_tensor_cores cannot see: unaligned pointers, scale <= 0, causal with Nq != Nkv (pure host functions)."""
+    b200_*_uses_tensor_cores cannot see: unaligned pointers, scale <= 0, fp32 causal backward (pure host functions)."""
     R = fa.lib.b200_fa2_fwd_route
     BF, F32 = 0, 1
     A = 4096                                   # a 16-byte aligned dummy address (never dereferenced)
@@ -126,10 +126,11 @@ def test_route_query_reports_the_demotions():
     assert R(A + 2, A, A, A, 8192, 8192, 128, 0.0, BF, 0) == 0        # unaligned Q
     assert R(A, A, A, A, 8192, 8192, 128, -1.0, BF, 0) == 0           # scale <= 0
     assert R(A, A, A, A, 1024, 1024, 128, 0.0, BF, 1) == 1            # causal, square
-    assert R(A, A, A, A, 512, 1024, 128, 0.0, BF, 1) == 0             # causal, cross lengths
+    assert R(A, A, A, A, 512, 1024, 128, 0.0, BF, 1) == 1             # causal, cross lengths (tensor cores since r2e)
     assert R(A, A, A, A, 1024, 512, 128, 0.0, BF, 1) == -1            # causal needs Nq <= Nkv
     Rb = fa.lib.b200_fa2_bwd_route
     assert Rb(A, A, A, A, A, A, A, 8192, 8192, 128, 0.0, BF, 0) == 1
     assert Rb(A, A, A, A, A, A, A + 4, 8192, 8192, 128, 0.0, BF, 0) == 0
-    assert Rb(A, A, A, A, A, A, A, 512, 1024, 128, 0.0, BF, 1) == 0
+    assert Rb(A, A, A, A, A, A, A, 512, 1024, 128, 0.0, BF, 1) == 1
+    assert Rb(A, A, A, A, A, A, A, 512, 1024, 64, 0.0, F32, 1) == 0         # fp32 causal backward: generic
     assert Rb(A, A, A, A, A, A, A, 128, 128, 64, 0.0, F32, 0) == fa.lib.b200_bwd_uses_tensor_cores(F32, 64, 128, 128)

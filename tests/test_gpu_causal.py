@@ -9,6 +9,7 @@ import torch
 
 import oracle
 import cuda_flashattention_b200 as fa
+from cuda_flashattention_b200._lib import lib
 from gpu_util import dev, host, rel_l2
 
 pytestmark = pytest.mark.gpu
@@ -41,22 +42,48 @@ def test_causal_forward_tensor_core(dtype, d, N):
 @pytest.mark.parametrize("dtype,d,Nq,Nkv", [
     (torch.float32, 32, 50, 50), (torch.float32, 96, 100, 260), (torch.bfloat16, 128, 200, 333),
     (torch.float32, 64, 1, 129), (torch.bfloat16, 64, 128, 640),
+    # r2e: cross-length causal runs on the tensor-core kernels too (chunked prefill / decode shapes)
+    (torch.bfloat16, 128, 256, 1024), (torch.bfloat16, 128, 1000, 1500), (torch.bfloat16, 128, 64, 2048), (torch.bfloat16, 128, 130, 131),
+    (torch.bfloat16, 64, 333, 1000), (torch.float32, 64, 300, 700), (torch.float32, 128, 100, 400),
 ])
 def test_causal_generic_and_bottom_right_alignment(dtype, d, Nq, Nkv):
-    # Nq < Nkv: query i sees keys 0 .. i + (Nkv - Nq); these shapes run on the CUDA-core kernels
+    # Nq < Nkv: query i sees keys 0 .. i + (Nkv - Nq) (bottom-right aligned).  d in {64, 128}: tensor-core kernels (fp32:
+    # tf32 forward, generic backward); other d: the CUDA-core kernels
     rng = np.random.default_rng(Nq * 3 + Nkv)
     q = _rand((Nq, d), rng, dtype)
     k, v = _rand((Nkv, d), rng, dtype), _rand((Nkv, d), rng, dtype)
     do = _rand((Nq, d), rng, dtype)
     O, L = fa.flash_attention_2_forward(q, k, v, 0.0, causal=True)
     Oo, Lo = oracle.forward(host(q), host(k), host(v), 0.0, causal=True)
-    tol = 2e-2 if dtype == torch.bfloat16 else 1e-4
+    tc = d in (64, 128)
+    assert lib.b200_fa2_fwd_route(q.data_ptr(), k.data_ptr(), v.data_ptr(), O.data_ptr(), Nq, Nkv, d, 0.0,
+                                  0 if dtype == torch.bfloat16 else 1, 1) == (1 if tc else 0)
+    tol = 2e-2 if dtype == torch.bfloat16 else (2e-3 if tc else 1e-4)      # bf16 / tf32 / exact fp32
     assert np.abs(host(O) - Oo).max() <= tol and np.abs(host(L) - Lo).max() <= tol
     dQ, dK, dV = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0, causal=True)
     ref = oracle.backward(host(q), host(k), host(v), host(do), 0.0, causal=True)
     for got, want in zip((dQ, dK, dV), ref):
         assert np.abs(host(got) - want).max() <= tol * max(1.0, float(np.abs(want).max()))
-        assert rel_l2(host(got), want) <= (1e-2 if dtype == torch.bfloat16 else 1e-4)
+        assert rel_l2(host(got), want) <= (1e-2 if dtype == torch.bfloat16 else (2e-3 if tc else 1e-4))
+
+
+def test_causal_cross_lengths_batched_tensor_core():
+    """Batched, several heads, Nq < Nkv with both ragged: every (b, h) slab against the oracle's causal rows."""
+    rng = np.random.default_rng(99)
+    B, H, Nq, Nkv, d = 2, 3, 300, 777, 128
+    q, do = _rand((B, H, Nq, d), rng, torch.bfloat16), _rand((B, H, Nq, d), rng, torch.bfloat16)
+    k, v = _rand((B, H, Nkv, d), rng, torch.bfloat16), _rand((B, H, Nkv, d), rng, torch.bfloat16)
+    O, L = fa.flash_attention_2_forward(q, k, v, 0.0, causal=True)
+    dQ, dK, dV = fa.flash_attention_2_backward(q, k, v, O, L, do, 0.0, causal=True)
+    for b in range(B):
+        for h in range(H):
+            Oo, Lo = oracle.forward(host(q[b, h]), host(k[b, h]), host(v[b, h]), 0.0, causal=True)
+            assert np.abs(host(O[b, h]) - Oo).max() <= 2e-2 and np.abs(host(L[b, h]) - Lo).max() <= 2e-2
+            ref = oracle.backward(host(q[b, h]), host(k[b, h]), host(v[b, h]), host(do[b, h]), 0.0, causal=True)
+            for name, got, want in zip(("dQ", "dK", "dV"), (dQ, dK, dV), ref):
+                g = host(got[b, h])
+                assert np.abs(g - want).max() <= 2e-2 * max(1.0, float(np.abs(want).max())), name
+                assert rel_l2(g, want) <= 1e-2, name
 
 
 def test_causal_needs_nq_le_nkv():
