@@ -10,6 +10,8 @@ mkdir -p gpurun_out
 out=gpurun_out/try_fwd_variant_$V.log
 : > $out
 [ -x build/kbench ] || nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -o build/kbench tools/kbench.cu -ldl
+# (the variants live in the side library only: make -C cuda_flashattention_b200 EXPERIMENTS=1)
+export B200ATTN_LIB=${B200ATTN_LIB:-cuda_flashattention_b200/libb200attn_exp.so}
 run() {
     echo "\$ $*" >> $out
     timeout 25 env "$@" >> $out 2>&1
