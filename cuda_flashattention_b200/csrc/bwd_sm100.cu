@@ -306,6 +306,8 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 //   * K^T resident in TMEM (M5 as a TS MMA) with S single-buffered: correct, level (the S -> P -> M3 -> M1 chain, ~2300 clk,
 //     replaces the pipe limit)
 //   * mbarrier.try_wait suspend hints: no effect                       (profiles/r2a_try_suspend_no_effect.txt)
+//   * dS hand-off split in two (TMEM copy ready -> M4 at once, shared-memory copy ready -> M5): level / -1 %
+//                                                                      (profiles/r2e_bwd_split_ds_handoff_level.txt)
 // The subtraction profile (profiles/r2a_bwd_subtraction_profile.txt) and tools/mma_rate.cu explain why: an SS MMA with
 // M = 128 costs >= 64 clk whatever N <= 128 is (the A tile is read from shared memory at 64 B/clk), so the three N = 64
 // SS groups cost 3 x 8 x 64 = 1536 clk and the two TS groups 512: 2048 clk per iteration against the measured ~2090.
