@@ -92,6 +92,7 @@ EXPORTS = tuple(_SIGS)
 
 B200_DTYPE_BF16 = 0
 B200_DTYPE_F32 = 1
+B200_DTYPE_FP8_E4M3 = 2
 
 
 class B200Error(RuntimeError):

@@ -12,10 +12,11 @@ torch is used only for device memory and streams.
         src/01_flash_attention_v1/main.cu:7
 
 Tensors are [N, d] (one head, the reference's shape) or [B, H, N, d]; fp32 or bf16; contiguous.
+The forward also takes torch.float8_e4m3fn Q/K/V (d = 128; O comes back in bf16).
 """
 import torch
 
-from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32, AttnDesc, Layout
+from ._lib import lib, check, B200_DTYPE_BF16, B200_DTYPE_F32, B200_DTYPE_FP8_E4M3, AttnDesc, Layout
 
 FLAG_CAUSAL = 1  # B200_FLAG_CAUSAL (include/b200attn.h)
 
@@ -25,7 +26,9 @@ def _dtype_code(t):
         return B200_DTYPE_F32
     if t.dtype == torch.bfloat16:
         return B200_DTYPE_BF16
-    raise TypeError(f"unsupported dtype {t.dtype}: fp32 and bf16 only")
+    if t.dtype == torch.float8_e4m3fn:
+        return B200_DTYPE_FP8_E4M3           # forward only, d = 128: fp8 Q/K/V in, bf16 O out
+    raise TypeError(f"unsupported dtype {t.dtype}: fp32, bf16 (and fp8 e4m3 for the forward) only")
 
 
 def _check_inputs(*ts):
@@ -59,7 +62,7 @@ def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True, causa
     Bk, Hk, Nkv, dk = _bhnd(K)
     if (Bk, Hk, dk) != (B, H, d) or tuple(V.shape) != tuple(K.shape):
         raise ValueError("Q/K/V shape mismatch")
-    O = torch.empty_like(Q)
+    O = torch.empty(Q.shape, dtype=torch.bfloat16 if Q.dtype == torch.float8_e4m3fn else Q.dtype, device=Q.device)
     L = torch.empty(Q.shape[:-1], dtype=torch.float32, device=Q.device)
     with torch.cuda.device(Q.device):
         check(lib.b200_fa2_fwd_ex(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(),

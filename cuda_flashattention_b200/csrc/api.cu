@@ -87,7 +87,7 @@ static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float*
 {
     const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
     if ((flags & ~B200_FLAG_CAUSAL) != 0 || (causal && Nq > Nkv)) return B200_ERR_INVALID_ARGUMENT;
-    if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
+    if (!(valid_dtype(dtype) || dtype == B200_DTYPE_FP8_E4M3) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (BH == 0 || Nq == 0) return B200_OK;
     if (Nkv == 0) return B200_ERR_INVALID_ARGUMENT;            // softmax over an empty set is undefined
     if (!Q || !K || !V || !O) return B200_ERR_INVALID_ARGUMENT;
@@ -96,6 +96,7 @@ static int fwd_impl(const void* Q, const void* K, const void* V, void* O, float*
     // tensor-core causal path: square problems (the usual self-attention case); everything else runs on the generic kernels
     if (fwd_routes_tc(Q, K, V, O, dtype, d, Nq, Nkv, scale, causal))
         return tc_fwd(Q, K, V, O, L, BH, Nq, Nkv, d, scale, dtype, st, causal);
+    if (dtype == B200_DTYPE_FP8_E4M3) return B200_ERR_UNSUPPORTED;        // fp8 exists on the tensor-core kernel only
     return simt_fwd(Q, K, V, O, L, nullptr, BH, Nq, Nkv, d, scale, dtype, 0, st, causal ? Nkv - Nq : kNoCausal);
 }
 
@@ -113,6 +114,7 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
 {
     const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
     if ((flags & ~B200_FLAG_CAUSAL) != 0 || (causal && Nq > Nkv)) return B200_ERR_INVALID_ARGUMENT;
+    if (dtype == B200_DTYPE_FP8_E4M3) return B200_ERR_UNSUPPORTED;         // forward-only dtype
     if (!valid_dtype(dtype) || BH < 0 || Nq < 0 || Nkv < 0 || d <= 0) return B200_ERR_INVALID_ARGUMENT;
     if (BH == 0 || (Nq == 0 && Nkv == 0)) return B200_OK;
     if (Nq == 0 || Nkv == 0) return B200_ERR_INVALID_ARGUMENT;
@@ -272,9 +274,11 @@ int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv)
 int b200_fa2_fwd_route(const void* Q, const void* K, const void* V, const void* O, int Nq, int Nkv, int d, float scale,
                        int dtype, int flags)
 {
-    if (!valid_dtype(dtype) || Nq < 1 || Nkv < 1 || d <= 0 || (flags & ~B200_FLAG_CAUSAL) != 0) return B200_ERR_INVALID_ARGUMENT;
+    if (!(valid_dtype(dtype) || dtype == B200_DTYPE_FP8_E4M3) || Nq < 1 || Nkv < 1 || d <= 0 || (flags & ~B200_FLAG_CAUSAL) != 0)
+        return B200_ERR_INVALID_ARGUMENT;
     const bool causal = (flags & B200_FLAG_CAUSAL) != 0;
     if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
+    if (dtype == B200_DTYPE_FP8_E4M3 && !fwd_routes_tc(Q, K, V, O, dtype, d, Nq, Nkv, resolve_scale(scale, d), causal)) return B200_ERR_UNSUPPORTED;
     return fwd_routes_tc(Q, K, V, O, dtype, d, Nq, Nkv, resolve_scale(scale, d), causal) ? B200_ROUTE_TENSOR_CORE : B200_ROUTE_GENERIC;
 }
 int b200_fa2_bwd_route(const void* Q, const void* K, const void* V, const void* dO, const void* dQ, const void* dK,

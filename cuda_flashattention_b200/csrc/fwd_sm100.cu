@@ -39,6 +39,13 @@ struct FwdCfg {
     using Elem = Elem_;
     static constexpr int EB = sizeof(Elem);
     static constexpr bool kF32 = (EB == 4);
+    // EB == 1: fp8 e4m3 operands (kind::f8f6f4, K = 32 per MMA), P written back to TMEM as e4m3 (4 per column), O stored
+    // as bf16 through its own staging tiles (a bf16 O tile is twice the bytes of an fp8 Q tile)
+    static constexpr bool kF8 = (EB == 1);
+    static constexpr int OEB = kF8 ? 2 : EB;               // bytes per output element
+    static constexpr int OCPB = 128 / OEB, O_BOXES = D_ / OCPB;
+    static constexpr int O_TILE = O_BOXES * 128 * 128;
+    static constexpr int O_STAGE = kF8 ? NT_ * O_TILE : 0;  // dedicated O staging (fp8 only), after the K/V stages
     static constexpr int D = D_, NT = NT_, BC = BC_, BR = 128, STAGES = 2;
     static constexpr int CPB = 128 / EB;                 // elements per 128-byte swizzle row ("box" width)
     static constexpr int KPER = 32 / EB;                 // K elements per tcgen05.mma (bf16: 16, tf32: 8)
@@ -54,14 +61,14 @@ struct FwdCfg {
     // setmaxnreg targets (warps 0-3 / softmax).  The pool is what the CTA got at launch -- 384 threads x 168
     // registers = 64512, not the whole 64K file -- and a setmaxnreg.inc that cannot be served waits forever.
     static constexpr int REGS_CTRL = 64, REGS_SOFTMAX = 216;
-    static constexpr int SMEM = 1024 + NT * Q_TILE + 2 * STAGES * KV_TILE + NBARS * 8 + 16;
-    static constexpr int PCOLS_PER_CHUNK = kF32 ? 32 : 16;   // TMEM columns written per 32 P values
+    static constexpr int SMEM = 1024 + NT * Q_TILE + 2 * STAGES * KV_TILE + O_STAGE + NBARS * 8 + 16;
+    static constexpr int PCOLS_PER_CHUNK = kF32 ? 32 : (kF8 ? 8 : 16);   // TMEM columns written per 32 P values
     // V is the MN-major B operand of O += P V.  bf16: plain 128B swizzle.  tf32: the hardware only
     // accepts the 32-byte-atom 128B swizzle for MN-major operands (4-row pattern, SBO = 512).
     static constexpr uint32_t V_LAYOUT = kF32 ? 1u : 2u;
     static constexpr uint32_t V_SBO = kF32 ? 512u : 1024u;
     static_assert(D % CPB == 0 && BC % 64 == 0 && BC <= 128 && D <= 128, "tile shape");
-    static_assert(POLY == 0 || !kF32, "the polynomial exp2 is only accurate enough for bf16 P");
+    static_assert(POLY == 0 || (!kF32 && !kF8), "the polynomial exp2 is only used for bf16 P");
     static_assert(NT != 2 || 128 * REGS_CTRL + 256 * REGS_SOFTMAX <= 384 * 168, "register pool of the CTA");
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
 };
@@ -72,13 +79,24 @@ __device__ __forceinline__ uint32_t cvt_tf32(float x) {
     return r;
 }
 
-template <bool F32>
+// element size -> MMA kind: 4 = tf32, 2 = f16 (bf16), 1 = f8f6f4 (e4m3)
+template <int EB>
 __device__ __forceinline__ void umma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, bool acc) {
-    if constexpr (F32) umma_tf32_ss(d, a, b, idesc, acc ? 1u : 0u); else umma_f16_ss(d, a, b, idesc, acc ? 1u : 0u);
+    if constexpr (EB == 4) umma_tf32_ss(d, a, b, idesc, acc ? 1u : 0u);
+    else if constexpr (EB == 1) umma_f8_ss(d, a, b, idesc, acc ? 1u : 0u);
+    else umma_f16_ss(d, a, b, idesc, acc ? 1u : 0u);
 }
-template <bool F32>
+template <int EB>
 __device__ __forceinline__ void umma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, bool acc) {
-    if constexpr (F32) umma_tf32_ts(d, a_tmem, b, idesc, acc ? 1u : 0u); else umma_f16_ts(d, a_tmem, b, idesc, acc ? 1u : 0u);
+    if constexpr (EB == 4) umma_tf32_ts(d, a_tmem, b, idesc, acc ? 1u : 0u);
+    else if constexpr (EB == 1) umma_f8_ts(d, a_tmem, b, idesc, acc ? 1u : 0u);
+    else umma_f16_ts(d, a_tmem, b, idesc, acc ? 1u : 0u);
+}
+// two fp32 -> two e4m3 in the low 16 bits (lo in bits 0..7)
+__device__ __forceinline__ uint32_t pack_e4m3x2(float lo, float hi) {
+    uint16_t r;
+    asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+    return r;
 }
 
 // Lazy-rescale threshold in log2 units: the running max is only refreshed (and O rescaled) when
@@ -145,9 +163,15 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
                     }
                     if (c == 0 && i < 4) acc[i] = f2_pack(p0, p1); else acc[i & 3] = f2_add(acc[i & 3], f2_pack(p0, p1));
                     if constexpr (C::kF32) { r[2 * i] = cvt_tf32(p0); r[2 * i + 1] = cvt_tf32(p1); }
+                    else if constexpr (C::kF8) {
+                        const uint32_t h2 = pack_e4m3x2(p0, p1);               // four P values per column
+                        if (i & 1) r[i >> 1] |= h2 << 16; else r[i >> 1] = h2;
+                    }
                     else r[i] = pack_bf16x2(p0, p1);
                 }
-                if constexpr (C::kF32) B200_TMEM_ST_32(tS + 32 * c, r); else B200_TMEM_ST_16(tS + 16 * c, r);
+                if constexpr (C::kF32) B200_TMEM_ST_32(tS + 32 * c, r);
+                else if constexpr (C::kF8) B200_TMEM_ST_8(tS + 8 * c, r);
+                else B200_TMEM_ST_16(tS + 16 * c, r);
             }
         };
         // Speculate: the first half of P is computed with the running max as it stands, while the row
@@ -211,7 +235,8 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     mbar_wait(bar_O, 0);
     tc_fence_after();
     const float inv_l = 1.0f / l;
-    uint8_t* sO = sQ + t * C::Q_TILE;
+    // (fp8: the bf16 O tile does not fit the fp8 Q tile; it has its own staging behind the K/V stages)
+    uint8_t* sO = C::kF8 ? sQ + C::NT * C::Q_TILE + 2 * C::STAGES * C::KV_TILE + t * C::O_TILE : sQ + t * C::Q_TILE;
     const int r = wg_thread;
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {
@@ -246,7 +271,7 @@ __device__ __forceinline__ void softmax_role(int t, uint32_t tmem, uint8_t* sQ, 
     named_bar_sync(1 + t, 128);
     if (wg_thread == 0) {
 #pragma unroll
-        for (int bx = 0; bx < C::BOXES; ++bx) tma_store_4d(tmO, sO + bx * C::Q_BOX, bx * C::CPB, q0 + t * 128, h, b);
+        for (int bx = 0; bx < C::O_BOXES; ++bx) tma_store_4d(tmO, sO + bx * C::Q_BOX, bx * C::OCPB, q0 + t * 128, h, b);
         tma_store_commit();
         tma_store_wait<0>();
     }
@@ -267,7 +292,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + NT * C::Q_TILE;
     uint8_t* sV = sK + ST * C::KV_TILE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ST * C::KV_TILE);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + ST * C::KV_TILE + C::O_STAGE);
     uint64_t* bar_Q = bars;                 // [NT]  Q tile landed
     uint64_t* bar_S = bar_Q + NT;           // [NT]  S_t(j) complete in TMEM
     uint64_t* bar_Pa = bar_S + NT;          // [NT]  first half of P_t(j) written (one arrival per softmax warp)
@@ -338,7 +363,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         reg_dec<C::REGS_CTRL>();
         const int t = warp == 1 ? 0 : 1;
         if (t < ntiles && elect_one()) {
-            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : kFmtBF16;
+            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : (C::kF8 ? kFmtE4M3 : kFmtBF16);
             constexpr uint32_t idesc_S = make_idesc(fmt, 128, BC, false, false);
             constexpr uint32_t idesc_PV = make_idesc(fmt, 128, D, false, true);
             const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV);
@@ -350,7 +375,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 #pragma unroll
                 for (int kk = 0; kk < D / C::KPER; ++kk) {
                     const uint32_t inbox = (kk & 3) * 32;
-                    umma_ss<C::kF32>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
+                    umma_ss<C::EB>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
                                      sdesc_advance(kd, (kk >> 2) * C::KV_BOX + inbox), idesc_S, kk > 0);
                 }
                 umma_commit(&bar_S[t]);
@@ -362,7 +387,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 #pragma unroll
                 for (int k2 = 0; k2 < KH; ++k2) {
                     const int kk = half * KH + k2;
-                    umma_ts<C::kF32>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
+                    umma_ts<C::EB>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
                                      sdesc_advance(vd, kk * C::KPER * 128), idesc_PV, (j > 0 || kk > 0));
                 }
             };
@@ -396,7 +421,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
         // ================================ MMA issuer ==================================
         if constexpr (NT == 2) reg_dec<C::REGS_CTRL>();
         if (elect_one()) {
-            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : kFmtBF16;
+            constexpr uint32_t fmt = C::kF32 ? kFmtTF32 : (C::kF8 ? kFmtE4M3 : kFmtBF16);
             constexpr uint32_t idesc_S = make_idesc(fmt, 128, BC, false, false);
             constexpr uint32_t idesc_PV = make_idesc(fmt, 128, D, false, true);
             const uint32_t q_base = smem_u32(sQ), k_base = smem_u32(sK), v_base = smem_u32(sV);
@@ -408,7 +433,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 #pragma unroll
                 for (int kk = 0; kk < D / C::KPER; ++kk) {
                     const uint32_t inbox = (kk & 3) * 32;
-                    umma_ss<C::kF32>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
+                    umma_ss<C::EB>(tmem + 128 * t, sdesc_advance(qd, (kk >> 2) * C::Q_BOX + inbox),
                                      sdesc_advance(kd, (kk >> 2) * C::KV_BOX + inbox), idesc_S, kk > 0);
                 }
                 umma_commit(&bar_S[t]);
@@ -420,7 +445,7 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 #pragma unroll
                 for (int k2 = 0; k2 < KH; ++k2) {
                     const int kk = half * KH + k2;
-                    umma_ts<C::kF32>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
+                    umma_ts<C::EB>(tmem + 256 + 128 * t, tmem + 128 * t + 8 * kk,
                                      sdesc_advance(vd, kk * C::KPER * 128), idesc_PV, (j > 0 || kk > 0));
                 }
             };
@@ -492,7 +517,8 @@ static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
         B200_CUDA_TRY(cudaFuncSetAttribute(fwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    const CUtensorMapDataType dt = C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType dt = C::kF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (C::kF8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+    const CUtensorMapDataType odt = C::kF8 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : dt;     // fp8 in, bf16 out
     const CUtensorMapSwizzle v_swz = C::kF32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     const float scale_log2 = a.scale * 1.4426950408889634f;
     CUtensorMap tmQ, tmK, tmV, tmO;
@@ -500,7 +526,7 @@ static int launch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
     if ((trc = make_tmap_4d(&tmQ, a.Q, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lq.sb, a.lq.sh, a.lq.sn, 128, C::CPB)) ||
         (trc = make_tmap_4d(&tmK, a.K, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lk.sb, a.lk.sh, a.lk.sn, C::BC, C::CPB)) ||
         (trc = make_tmap_4d(&tmV, a.V, dt, C::EB, a.B, a.Hkv, a.Nkv, C::D, a.lv.sb, a.lv.sh, a.lv.sn, C::BC, C::CPB, v_swz)) ||
-        (trc = make_tmap_4d(&tmO, a.O, dt, C::EB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::CPB)))
+        (trc = make_tmap_4d(&tmO, a.O, odt, C::OEB, a.B, a.H, a.Nq, C::D, a.lo.sb, a.lo.sh, a.lo.sn, 128, C::OCPB)))
         return trc == -2 ? B200_ERR_UNSUPPORTED : B200_ERR_CUDA;   // -2: a stride is zero or not a multiple of 16 bytes
     dim3 grid((a.Nq + C::NT * 128 - 1) / (C::NT * 128), a.H, a.B);
     fwd_kernel<C><<<grid, C::THREADS, C::SMEM, st>>>(tmQ, tmK, tmV, tmO, a.L, a.ldL, a.Nq, a.Nkv, scale_log2, a.causal ? 1 + (a.Nkv - a.Nq) : 0,
@@ -522,6 +548,7 @@ int fwd_trace_read(long long* out, int n)
 bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
 {
     if (Nq < 1 || Nkv < 1) return false;
+    if (dtype == B200_DTYPE_FP8_E4M3) return d == 128;         // forward only: fp8 Q/K/V in, bf16 O out
     if (dtype != B200_DTYPE_BF16 && dtype != B200_DTYPE_F32) return false;
     return d == 64 || d == 128;
 }
@@ -534,8 +561,11 @@ bool tc_fwd_supported(int dtype, int d, int Nq, int Nkv)
 // The measured-negative variants (split-S, CTA pairs, shared score buffer, two issuers on this kernel, POLY / SPLITP
 // sweeps) live in csrc/experiments/ and are only compiled into `make EXPERIMENTS=1` side libraries, where
 // B200_FWD_VARIANT selects them for A/B timing; the product library has no environment hooks.
+struct fp8_e4m3_t { uint8_t x; };       // (an 8-bit element tag for FwdCfg; the kernel never does arithmetic on it)
+
 static int dispatch_fwd(const FwdArgs& a, int BH_valid, cudaStream_t st)
 {
+    if (a.dtype == B200_DTYPE_FP8_E4M3) return launch_fwd<FwdCfg<fp8_e4m3_t, 128, 2, 128>>(a, BH_valid, st);
     if (a.dtype == B200_DTYPE_BF16) {
         if (a.d == 128) {
 #ifdef B200_EXPERIMENTS

@@ -210,10 +210,24 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, u
         ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+// kind::f8f6f4 (fp8 e4m3 / e5m2 operands, K = 32 per instruction, fp32 accumulation)
+__device__ __forceinline__ void umma_f8_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_f8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], %2, %3, p;\n\t}\n"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
 // Instruction descriptor (32 bit).  Fields: [4,6) D format (1 = f32); [7,10) A format, [10,13) B format
 // (kind::f16: 0 = f16, 1 = bf16; kind::tf32: 2 = tf32); [13] negate A; [14] negate B;
 // [15] A major (0 = K-major, 1 = MN-major); [16] B major; [17,23) N>>3; [24,29) M>>4.
-enum : uint32_t { kFmtF16 = 0, kFmtBF16 = 1, kFmtTF32 = 2 };
+enum : uint32_t { kFmtF16 = 0, kFmtBF16 = 1, kFmtTF32 = 2, kFmtE4M3 = 0, kFmtE5M2 = 1 };   // (E4M3 / E5M2: kind::f8f6f4)
 __host__ __device__ constexpr uint32_t make_idesc(uint32_t fmt_ab, int M, int N, bool a_mn_major, bool b_mn_major) {
     return (1u << 4) | (fmt_ab << 7) | (fmt_ab << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
            (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
@@ -281,6 +295,11 @@ __host__ __device__ constexpr uint64_t sdesc_advance(uint64_t desc, uint32_t byt
                    "r"((r)[5]), "r"((r)[6]), "r"((r)[7]), "r"((r)[8]), "r"((r)[9]), "r"((r)[10]),         \
                    "r"((r)[11]), "r"((r)[12]), "r"((r)[13]), "r"((r)[14]), "r"((r)[15])                   \
                  : "memory")
+
+#define B200_TMEM_ST_8(taddr, r)                                                                          \
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"                 \
+                 ::"r"(taddr), "r"((r)[0]), "r"((r)[1]), "r"((r)[2]), "r"((r)[3]), "r"((r)[4]),           \
+                   "r"((r)[5]), "r"((r)[6]), "r"((r)[7]) : "memory")
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t r;

@@ -64,7 +64,12 @@ typedef enum {
 
 typedef enum {
     B200_DTYPE_BF16 = 0,         /* bf16 I/O, bf16 tensor-core operands, fp32 accumulation */
-    B200_DTYPE_F32 = 1           /* fp32 I/O (the reference's type), tf32 tensor-core operands, fp32 accumulation */
+    B200_DTYPE_F32 = 1,          /* fp32 I/O (the reference's type), tf32 tensor-core operands, fp32 accumulation */
+    B200_DTYPE_FP8_E4M3 = 2      /* FORWARD ONLY, d = 128: Q, K, V are fp8 e4m3 bytes, O is bf16, L fp32; kind::f8f6f4
+                                  * tensor-core operands, P rounded to e4m3, fp32 accumulation.  Unit scales: fold any
+                                  * per-tensor dequantisation of Q / K into `scale` and apply V's to O.  Calls that the fp8
+                                  * kernel cannot take (other d, unaligned pointers, backward, ring) return
+                                  * B200_ERR_UNSUPPORTED -- there is no generic fp8 path. */
 } b200_dtype;
 
 B200_API const char* b200_strerror(int status);

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <vector>
 #include <cmath>
+#include <cuda_fp8.h>
 #include "../cuda_flashattention_b200/csrc/ptx.cuh"
 #include "../cuda_flashattention_b200/csrc/tmap.h"
 
@@ -75,6 +76,14 @@ probe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     r[i] = pack_bf16x2(__bfloat162float(a[2 * (c0 + i)]), __bfloat162float(a[2 * (c0 + i) + 1]));
                 B200_TMEM_ST_16(lane_addr + c0, r);
             }
+        } else if (p.elem_bytes == 1) {
+            // fp8: four K elements per 32-bit column, lowest K index in the lowest byte
+            const uint32_t* a = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(p.A_gmem) + (size_t)tid * p.Ktot);
+            for (int c0 = 0; c0 < p.Ktot / 4; c0 += 16) {
+                uint32_t r[16];
+                for (int i = 0; i < 16; ++i) r[i] = a[c0 + i];
+                B200_TMEM_ST_16(lane_addr + c0, r);
+            }
         } else {
             const float* a = reinterpret_cast<const float*>(p.A_gmem) + (size_t)tid * p.Ktot;
             for (int c0 = 0; c0 < p.Ktot; c0 += 16) {
@@ -111,10 +120,12 @@ probe_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             if (p.a_mode == 1) {
                 uint32_t at = tmem_A + s * p.a_tmem_cols_per_step;
                 if (p.elem_bytes == 2) umma_f16_ts(tmem_D, at, bd, p.idesc, s > 0);
+                else if (p.elem_bytes == 1) umma_f8_ts(tmem_D, at, bd, p.idesc, s > 0);
                 else                   umma_tf32_ts(tmem_D, at, bd, p.idesc, s > 0);
             } else {
                 uint64_t ad = sdesc_advance(adesc0, aoff);
                 if (p.elem_bytes == 2) umma_f16_ss(tmem_D, ad, bd, p.idesc, s > 0);
+                else if (p.elem_bytes == 1) umma_f8_ss(tmem_D, ad, bd, p.idesc, s > 0);
                 else                   umma_tf32_ss(tmem_D, ad, bd, p.idesc, s > 0);
             }
         }
@@ -183,6 +194,12 @@ int main(int argc, char** argv)
         {"tf32 NT  SS  B K-major ATOM_32B SBO=512     ", 4, 0, false, false, 128, 64, false, false, 0, 0, 512},
         {"tf32 NT  SS  N=64 A,B K-major ATOM_32B      ", 4, 0, false, false, 64, 64, false, false, 0, 1024, 1024},
         {"tf32 TT  SS  N=64 A,B MN-major ATOM_32B 512 ", 4, 0, true, true, 64, 128, false, false, 512},
+        // r2 (fp8 forward, kind::f8f6f4 e4m3): K-major, MN-major B (the V operand of O += P V), A from TMEM (P)
+        {"fp8  NT  SS  (S=QK^T)            N=128 K=128", 1, 0, false, false, 128, 128, false, false},
+        {"fp8  NN  SS  (V MN-major)        N=128 K=128", 1, 0, false, true, 128, 128, false, false},
+        {"fp8  NN  TS  (P in TMEM, V MN)   N=128 K=128", 1, 1, false, true, 128, 128, false, false},
+        {"fp8  NN  SS  V MN-major, LBO/SBO swapped    ", 1, 0, false, true, 128, 128, false, true},
+        {"fp8  NT  TS  (P in TMEM, B K-major)   K=128 ", 1, 1, false, false, 128, 128, false, false},
     };
     const int ncases = sizeof(cases) / sizeof(cases[0]);
     if (argc < 2) { printf("%d\n", ncases); return 0; }
@@ -204,7 +221,8 @@ int main(int argc, char** argv)
         for (int r = 0; r < rows; ++r)
             for (int cc = 0; cc < cols; ++cc) {
                 float v = mn_major ? X[(size_t)cc * K + r] : X[(size_t)r * K + cc];
-                if (eb == 2) { __nv_bfloat16 h = __float2bfloat16(v); memcpy(&out[((size_t)r * cols + cc) * 2], &h, 2); }
+                if (eb == 1) { out[(size_t)r * cols + cc] = (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3); }
+                else if (eb == 2) { __nv_bfloat16 h = __float2bfloat16(v); memcpy(&out[((size_t)r * cols + cc) * 2], &h, 2); }
                 else memcpy(&out[((size_t)r * cols + cc) * 4], &v, 4);
             }
     };
@@ -219,7 +237,7 @@ int main(int argc, char** argv)
     CK(cudaMemset(dD, 0xff, (size_t)M * N * 4));
 
     CUtensorMap tmA, tmB;
-    CUtensorMapDataType dt = eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    CUtensorMapDataType dt = eb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
     CUtensorMapSwizzle swA = ((c.atom32 && c.a_mn) || c.atomk_a) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     CUtensorMapSwizzle swB = ((c.atom32 && c.b_mn) || c.atomk_b) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
     if (make_tmap_3d(&tmA, dA, dt, eb, 1, ar, ac, ar, cpb, swA) || make_tmap_3d(&tmB, dB, dt, eb, 1, br, bc, br, cpb, swB)) {
@@ -247,7 +265,7 @@ int main(int argc, char** argv)
     if (c.atomk_a && !c.a_mn) { p.a_layout = 1; p.a_sbo = c.atomk_a; }
     if (c.atomk_b && !c.b_mn) { p.b_layout = 1; p.b_sbo = c.atomk_b; }
     p.a_tmem_cols_per_step = 8;    // bf16: 16 K-elements packed 2/column; tf32: 8 K-elements 1/column
-    p.idesc = make_idesc(eb == 2 ? kFmtBF16 : kFmtTF32, M, N, c.a_mn, c.b_mn);
+    p.idesc = make_idesc(eb == 1 ? kFmtE4M3 : eb == 2 ? kFmtBF16 : kFmtTF32, M, N, c.a_mn, c.b_mn);
 
     const int smem_bytes = 131072 + 1024;
     CK(cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
