@@ -65,6 +65,7 @@ _SIGS = {
     "b200_fa2_fwd_bwd_host": (_i, [_vp] * 9 + [_i, _i, _i, _i, _f, _i, _vp]),
     "b200_fa2_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "b200_fa2_bwd": (_i, [_vp] * 9 + [_i, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
+    "b200_fa2_bwd_static": (_i, [_vp] * 9 + [_i, _i, _i, _i, _i, _f, _i, _vp]),
     "b200_rowdot": (_i, [_vp, _vp, _fp, _i, _i, _i, _i, _i, _vp]),
     "b200_lse_merge": (_i, [_vp, _fp, _vp, _fp, _i, _i, _i, _i, _i, _vp]),
     "b200_ring_kv_block": (_i, [_i, _i, _i]),
@@ -93,6 +94,7 @@ EXPORTS = tuple(_SIGS)
 B200_DTYPE_BF16 = 0
 B200_DTYPE_F32 = 1
 B200_DTYPE_FP8_E4M3 = 2
+B200_STATIC_SCRATCH_BYTES = 32 << 20     # include/b200attn.h
 
 
 class B200Error(RuntimeError):

@@ -197,6 +197,22 @@ B200_API int b200_fa2_bwd(const void* Q, const void* K, const void* V, const voi
                  void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
                  void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+/* b200_fa2_bwd for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and
+ * results as b200_fa2_bwd without the workspace pair: the scratch is a file-scope device array of
+ * B200_STATIC_SCRATCH_BYTES inside the library (csrc/static_scratch.cu), held by every GPU that loads the library until
+ * the process exits.  The call runs no cudaMalloc / cudaFree / allocating library routine; its first use on a device
+ * looks the array's address up (cudaGetSymbolAddress), so make one call per device before starting a capture.
+ * Problems whose b200_fa2_bwd_workspace_bytes() exceeds B200_STATIC_SCRATCH_BYTES are rejected with
+ * B200_ERR_WORKSPACE and nothing is launched (32 MiB covers e.g. bf16 B*H = 8, N = 4096, d = 128).
+ * All calls on a device share the one array, which keeps the previous call's contents; the call itself rewrites or
+ * zeroes what it reads, so calls ordered on the device are independent, but calls that OVERLAP on the GPU (different
+ * streams without an event between them) race on it -- use b200_fa2_bwd with one workspace per stream for those. */
+#define B200_STATIC_SCRATCH_BYTES (32u << 20)
+B200_API int b200_fa2_bwd_static(const void* Q, const void* K, const void* V, const void* O, const float* L, const void* dO,
+                        void* dQ, void* dK, void* dV, int B, int H, int Nq, int Nkv, int d, float scale, int dtype,
+                        cudaStream_t stream);
+
 /* D[b,h,i] = sum_c dO[b,h,i,c] * O[b,h,i,c]   (reference flash_attention_backward_kernel.cu:97-120) */
 B200_API int b200_rowdot(const void* dO, const void* O, float* D, int B, int H, int N, int d, int dtype, cudaStream_t stream);
 
