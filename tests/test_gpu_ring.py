@@ -61,3 +61,40 @@ def test_ring_nccl_multi_gpu():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     print(r.stdout[-3000:], r.stderr[-3000:])
     assert r.returncode == 0 and "RING_OK" in r.stdout
+
+
+def test_single_rank_communicator_bootstrap_exchange_and_ring_calls():
+    """The NCCL side of the ring on the one GPU a test box has: b200_ring_unique_id -> b200_ring_comm_init (a real
+    1-rank communicator, init_nccl_comm src/util/nccl_utils.h:62-103), b200_ring_exchange_kv to itself (the grouped
+    send(next)/recv(prev) of ring_exchange_kv, nccl_utils.h:133-142, with next = prev = 0), the ring calls on that
+    communicator, b200_ring_comm_destroy."""
+    import ctypes as C
+    lib = fa.lib
+    idbuf = (C.c_ubyte * 128)()
+    assert lib.b200_ring_unique_id(idbuf) == 0
+    assert any(idbuf)
+    comm = C.c_void_p(None)
+    assert lib.b200_ring_comm_init(C.byref(comm), idbuf, 0, 1) == 0 and comm.value
+    try:
+        rng = np.random.default_rng(11)
+        N, d = 640, 128
+        q, k, v, do = [dev(rng.standard_normal((1, 2, N, d)).astype(np.float32), torch.bfloat16) for _ in range(4)]
+        kr, vr = torch.zeros_like(k), torch.zeros_like(v)
+        st = torch.cuda.current_stream().cuda_stream
+        assert lib.b200_ring_exchange_kv(k.data_ptr(), kr.data_ptr(), v.data_ptr(), vr.data_ptr(), k.numel() * 2, 0, 0, comm, st) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(kr, k) and torch.equal(vr, v)
+        rc = fa.RingComm(rank=0, nranks=1)
+        rc.handle = comm
+        O, L = fa.ring_attention_forward(q, k, v, rc)
+        dQ, dK, dV = fa.ring_attention_backward(q, k, v, O, L, do, rc)
+        O1, L1 = fa.flash_attention_2_forward(q, k, v, 0.0)
+        g1 = fa.flash_attention_2_backward(q, k, v, O1, L1, do, 0.0)
+        torch.cuda.synchronize()
+        assert torch.equal(O, O1) and torch.equal(L, L1)
+        for a, b in zip((dQ, dK, dV), g1):
+            assert np.abs(host(a) - host(b)).max() <= 2e-2
+        want, _ = oracle.forward(host(q[0, 1]), host(k[0, 1]), host(v[0, 1]), 0.0)
+        assert np.abs(host(O[0, 1]) - want).max() <= 2e-2
+    finally:
+        assert lib.b200_ring_comm_destroy(comm) == 0
