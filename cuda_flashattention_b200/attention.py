@@ -74,9 +74,12 @@ def flash_attention_2_forward(Q, K, V, softmax_scale=0.0, return_lse=True, causa
 def flash_attention_2_backward(Q, K, V, O, L, dO, softmax_scale=0.0, causal=False):
     _check_inputs(Q, K, V, O, dO)
     B, H, Nq, d = _bhnd(Q)
-    _, _, Nkv, _ = _bhnd(K)
-    if L.dtype != torch.float32 or not L.is_contiguous():
-        raise ValueError("L must be contiguous fp32")
+    Bk, Hk, Nkv, dk = _bhnd(K)
+    if (Bk, Hk, dk) != (B, H, d) or tuple(V.shape) != tuple(K.shape) or tuple(O.shape) != tuple(Q.shape) or \
+            tuple(dO.shape) != tuple(Q.shape):
+        raise ValueError("Q/K/V/O/dO shape mismatch")
+    if L.dtype != torch.float32 or not L.is_contiguous() or L.device != Q.device or L.numel() != B * H * Nq:
+        raise ValueError("L must be contiguous fp32 [.., N] on the tensors' device")
     dQ, dK, dV = torch.empty_like(Q), torch.empty_like(K), torch.empty_like(V)
     with torch.cuda.device(Q.device):
         check(lib.b200_fa2_bwd_ex(Q.data_ptr(), K.data_ptr(), V.data_ptr(), O.data_ptr(), L.data_ptr(), dO.data_ptr(),
@@ -104,6 +107,9 @@ def lse_merge_(Oa, La, Ob, Lb):
     """In place on (Oa, La): merge two normalised partials by log-sum-exp."""
     _check_inputs(Oa, Ob)
     B, H, N, d = _bhnd(Oa)
+    if tuple(Ob.shape) != tuple(Oa.shape) or any(
+            t.dtype != torch.float32 or not t.is_contiguous() or t.device != Oa.device or t.numel() != B * H * N for t in (La, Lb)):
+        raise ValueError("lse_merge_: Ob must match Oa; La / Lb must be contiguous fp32 [.., N] on the same device")
     with torch.cuda.device(Oa.device):
         check(lib.b200_lse_merge(Oa.data_ptr(), La.data_ptr(), Ob.data_ptr(), Lb.data_ptr(), B, H, N, d,
                                  _dtype_code(Oa), _stream()), "b200_lse_merge")

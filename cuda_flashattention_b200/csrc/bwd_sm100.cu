@@ -308,6 +308,11 @@ __device__ __forceinline__ void bwd_epilogue(int w, uint32_t tmem, uint8_t* smem
 //   * mbarrier.try_wait suspend hints: no effect                       (profiles/r2a_try_suspend_no_effect.txt)
 //   * dS hand-off split in two (TMEM copy ready -> M4 at once, shared-memory copy ready -> M5): level / -1 %
 //                                                                      (profiles/r2e_bwd_split_ds_handoff_level.txt)
+//   * M1 issued for PAIRS of q tiles (one N = 128 group into S[0] | S[1], Q slots box-major so that two tiles form one
+//     128-row operand, dS single-buffered to pay for the fourth Q slot): correct on every tail, -6 % (11.6-11.7 against
+//     10.9-11.1 ms): the scores of a pair can only be issued after P of its second tile is consumed, which puts the
+//     compute warps on the critical path, and the N = 128 bursts starve their shared-memory loads / stores
+//                                                                      (profiles/r2h_bwd_paired_m1_negative.txt, .patch)
 // The subtraction profile (profiles/r2a_bwd_subtraction_profile.txt) and tools/mma_rate.cu explain why: an SS MMA with
 // M = 128 costs >= 64 clk whatever N <= 128 is (the A tile is read from shared memory at 64 B/clk), so the three N = 64
 // SS groups cost 3 x 8 x 64 = 1536 clk and the two TS groups 512: 2048 clk per iteration against the measured ~2090.
