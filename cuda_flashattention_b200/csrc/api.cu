@@ -65,7 +65,7 @@ static inline float resolve_scale(float s, int d) { return s == 0.0f ? 1.0f / sq
 
 // The routing predicates, shared by the calls and by b200_fa2_fwd_route / b200_fa2_bwd_route so that what a caller is
 // told is what runs.  Tensor-core path: supported (dtype, d), 16-byte aligned bases (TMA), scale > 0 (the forward folds
-// scale into the running max); the fp32 (tf32) backward is d = 64, non-causal.  Everything else: generic CUDA-core kernels.
+// scale into the running max); the fp32 (tf32) backward is d = 64.  Everything else: generic CUDA-core kernels.
 static bool fwd_routes_tc(const void* Q, const void* K, const void* V, const void* O, int dtype, int d, int Nq, int Nkv,
                           float scale, bool causal)
 {
@@ -78,7 +78,8 @@ static bool bwd_routes_tc(const void* Q, const void* K, const void* V, const voi
 {
     const uintptr_t al = (uintptr_t)Q | (uintptr_t)K | (uintptr_t)V | (uintptr_t)dO | (uintptr_t)dQ | (uintptr_t)dK | (uintptr_t)dV;
     if (g_force_generic || (al & 15) != 0) return false;
-    if (tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) return !causal;            // fp32 I/O: tf32 kernel, non-causal only
+    (void)causal;                                                            // (causal runs on both tensor-core backwards)
+    if (tc_bwd_tf32_supported(dtype, d, Nq, Nkv)) return true;               // fp32 I/O, d = 64: tf32 kernel
     return tc_bwd_supported(dtype, d, Nq, Nkv);
 }
 
@@ -129,7 +130,8 @@ static int bwd_impl(const void* Q, const void* K, const void* V, const void* O, 
     B200_TRY(rowdot(dO, O, D, (size_t)BH * Nq, d, dtype, st));
     if (bwd_routes_tc(Q, K, V, dO, dQ, dK, dV, dtype, d, Nq, Nkv, causal)) {
         if (dtype == B200_DTYPE_F32)
-            return tc_bwd_tf32(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, scale, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st);
+            return tc_bwd_tf32(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, scale, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st,
+                               causal);
         return tc_bwd(Q, K, V, dO, L, D, dQ, dK, dV, BH, Nq, Nkv, d, scale, dtype,
                       reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st, causal);
     }

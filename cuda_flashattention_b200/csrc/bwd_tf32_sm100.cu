@@ -81,7 +81,7 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
                 const __grid_constant__ CUtensorMap tmdOm, const __grid_constant__ CUtensorMap tmdK,
                 const __grid_constant__ CUtensorMap tmdV, float* __restrict__ dQ, const float* __restrict__ L2p,
-                const float* __restrict__ Dp, int Nq, int stat_stride, float scale_log2, float scale, int BH, int dbg)
+                const float* __restrict__ Dp, int Nq, int stat_stride, float scale_log2, float scale, int BH, int dbg, int causal)
 {
     using namespace bwt;
     (void)dbg;
@@ -105,7 +105,11 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const size_t bh = (size_t)b * gridDim.y + h;
     if (bh >= (size_t)BH) return;
     const int n_q = (Nq + BM - 1) / BM;
-    const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x) % n_q;     // staggered start: see bwd_sm100.cu
+    // causal = 1 + (Nkv - Nq) (bottom-right aligned mask, as in bwd_sm100.cu) or 0: the q tiles before the diagonal see none
+    // of this CTA's keys and are skipped; the tiles that cross it are masked in the compute warps
+    const int qt_min = causal ? min(max(kv0 - (causal - 1), 0) / BM, n_q - 1) : 0;
+    const int n_it = n_q - qt_min;
+    const int i_off = (int)(((long long)blockIdx.x * n_q) / gridDim.x) % n_it;    // staggered start: see bwd_sm100.cu
 
     if (threadIdx.x == 0) {
         mbar_init(bar_KV, 1);
@@ -134,10 +138,11 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             }
             const float* Lrow = L2p + bh * stat_stride;
             const float* Drow = Dp + bh * stat_stride;
-            for (int i = 0; i < n_q; ++i) {
+            for (int i = 0; i < n_it; ++i) {
                 const int s = i % NS;
                 int qt = i + i_off;
-                if (qt >= n_q) qt -= n_q;
+                if (qt >= n_it) qt -= n_it;
+                qt += qt_min;
                 mbar_wait(&bar_in_empty[s], ((i / NS) & 1) ^ 1);
                 mbar_expect_tx(&bar_in_full[s], (BWT_DBG(1024) ? 2 : 4) * Q_TILE + (BWT_DBG(512) ? 0 : 2 * STAT_BYTES));
                 for (int bx = 0; bx < 2; ++bx) {
@@ -181,9 +186,9 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             mbar_wait(&bar_in_full[0], 0);
             tc_fence_after();
             M1(0); M2(0);
-            for (int i = 0; i < n_q; ++i) {
+            for (int i = 0; i < n_it; ++i) {
                 const int bb = i & 1, s = i % NS;
-                if (i + 1 < n_q) {
+                if (i + 1 < n_it) {
                     mbar_wait(&bar_in_full[(i + 1) % NS], ((i + 1) / NS) & 1);
                     tc_fence_after();
                     M1(i + 1);
@@ -195,7 +200,7 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 tc_fence_after();
                 mma_ts(TM_DP, sb + OFF_QM + s * Q_TILE, TM_DK, i > 0);                  // M4: dK += dS^T Q_i
                 umma_commit(&bar_in_empty[s]);
-                if (i + 1 < n_q) M2(i + 1);
+                if (i + 1 < n_it) M2(i + 1);
                 mbar_wait(bar_dQ_empty, (i & 1) ^ 1);
                 tc_fence_after();
                 if (!BWT_DBG(4)) {                                                      // M5: dQ_i^T = K^T dS
@@ -216,7 +221,7 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t lane_base = uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16;
         const bool lane0 = (threadIdx.x & 31) == 0;
         const uint32_t stat_base = smem_u32(smem + OFF_STAT) + 64 * w;
-        for (int i = 0; i < n_q; ++i) {
+        for (int i = 0; i < n_it; ++i) {
             const int bb = i & 1, s = i % NS;
             const uint32_t tS = tmem + TM_S + 32 * bb + 16 * w + lane_base;
             const uint32_t tP = tmem + TM_DP + 16 * w + lane_base;
@@ -234,8 +239,19 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
                 p[c] = fast_exp2(fmaf(__uint_as_float(sv[c]), scale_log2, -st[c]));
-                pk[c] = to_tf32(p[c]);
             }
+            if (causal) {
+                // key kv0 + r is visible to the queries q >= kv0 + r - (Nkv - Nq): zero the columns before it (dS inherits the zeros)
+                int qt = i + i_off;
+                if (qt >= n_it) qt -= n_it;
+                const int first_visible = kv0 + r - (causal - 1) - (qt_min + qt) * BM - 16 * w;
+                if (first_visible > 0) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) if (c < first_visible) p[c] = 0.0f;
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 16; ++c) pk[c] = to_tf32(p[c]);
             B200_TMEM_ST_16(tS, pk);
 #pragma unroll
             for (int c = 0; c < 4; ++c) bwt_lds_f32x4(st + 4 * c, stat_base + s * 2 * STAT_BYTES + STAT_BYTES + 16 * c);   // D_i
@@ -296,9 +312,10 @@ bwd_tf32_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int r = threadIdx.x & 127;                                   // d index == TMEM lane (64 real)
         const uint32_t tQ = tmem + TM_DQ + (uint32_t(((threadIdx.x >> 5) & 3) * 32) << 16);
         const bool lane0 = (threadIdx.x & 31) == 0, leader = r == 0;
-        for (int i = 0; i < n_q; ++i) {
+        for (int i = 0; i < n_it; ++i) {
             int qt = i + i_off;
-            if (qt >= n_q) qt -= n_q;
+            if (qt >= n_it) qt -= n_it;
+            qt += qt_min;
             mbar_wait(bar_dQ_full, i & 1);
             tc_fence_after();
             uint32_t v[32];
@@ -363,7 +380,7 @@ size_t tc_bwd_tf32_workspace_bytes(int BH, int Nq, int Nkv)
 // L2p / Dp: padded statistics as in bwd_sm100.cu (pad = (+inf, 0): padded query rows contribute exactly 0); dQ must be
 // zeroed by the caller of this function on the same stream (the kernel add-reduces into it).
 int tc_bwd_tf32_launch(const float* Q, const float* K, const float* V, const float* dO, const float* L2p, const float* Dp,
-                       float* dQ, float* dK, float* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st)
+                       float* dQ, float* dK, float* dV, int BH, int Nq, int Nkv, float scale, cudaStream_t st, bool causal)
 {
     using namespace bwt;
     static bool attr_set[64] = {};
@@ -398,7 +415,7 @@ int tc_bwd_tf32_launch(const float* Q, const float* K, const float* V, const flo
     const int dbg = 0;
 #endif
     bwd_tf32_kernel<<<grid, THREADS, SMEM, st>>>(tmQ, tmQm, tmK, tmKm, tmV, tmdO, tmdOm, tmdK, tmdV, dQ, L2p, Dp, Nq, Nq_pad,
-                                                 scale * 1.4426950408889634f, scale, BH, dbg);
+                                                 scale * 1.4426950408889634f, scale, BH, dbg, causal ? 1 + (Nkv - Nq) : 0);
     B200_CUDA_TRY(cudaGetLastError());
     count_launch();
     return B200_OK;
@@ -407,8 +424,10 @@ int tc_bwd_tf32_launch(const float* Q, const float* K, const float* V, const flo
 
 // D = rowsum(dO o O) is in `Dvec`; `ws` as tc_bwd_tf32_workspace_bytes
 int tc_bwd_tf32(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* Dvec,
-                void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, void* ws, size_t ws_bytes, cudaStream_t st)
+                void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, void* ws, size_t ws_bytes, cudaStream_t st,
+                bool causal)
 {
+    if (causal && Nq > Nkv) return B200_ERR_INVALID_ARGUMENT;
     if (ws_bytes < tc_bwd_tf32_workspace_bytes(BH, Nq, Nkv)) return B200_ERR_WORKSPACE;
     const size_t Nq_pad = (size_t)(Nq + 63) / 64 * 64;
     const size_t nq = (size_t)BH * Nq * bwt::D, nk = (size_t)BH * Nkv * bwt::D;
@@ -432,7 +451,7 @@ int tc_bwd_tf32(const void* Q, const void* K, const void* V, const void* dO, con
     }
     B200_CUDA_TRY(cudaMemsetAsync(dQ, 0, nq * sizeof(float), st));
     return tc_bwd_tf32_launch(Qr, Kr, Vr, dOr, L2p, Dp, reinterpret_cast<float*>(dQ), reinterpret_cast<float*>(dK),
-                              reinterpret_cast<float*>(dV), BH, Nq, Nkv, scale, st);
+                              reinterpret_cast<float*>(dV), BH, Nq, Nkv, scale, st, causal);
 }
 
 }  // namespace b200

@@ -88,11 +88,12 @@ int tc_bwd(const void* Q, const void* K, const void* V, const void* dO, const fl
            void* ws, size_t ws_bytes, cudaStream_t st, bool causal = false);
 int tc_bwd_strided(const BwdArgs& a, void* ws, size_t ws_bytes, cudaStream_t st);
 
-// fp32 I/O backward on tf32 tensor cores (bwd_tf32_sm100.cu): d = 64, contiguous, non-causal
+// fp32 I/O backward on tf32 tensor cores (bwd_tf32_sm100.cu): d = 64, contiguous
 bool tc_bwd_tf32_supported(int dtype, int d, int Nq, int Nkv);
 size_t tc_bwd_tf32_workspace_bytes(int BH, int Nq, int Nkv);
 int tc_bwd_tf32(const void* Q, const void* K, const void* V, const void* dO, const float* L, const float* D,
-                void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, void* ws, size_t ws_bytes, cudaStream_t st);
+                void* dQ, void* dK, void* dV, int BH, int Nq, int Nkv, float scale, void* ws, size_t ws_bytes, cudaStream_t st,
+                bool causal = false);
 int pad_stats(const float* L, const float* D, float* L2p, float* Dp, int BH, int Nq, cudaStream_t st);
 
 // ring backward building blocks (bf16, d = 128): padded statistics once, then accumulate-only steps

@@ -83,7 +83,7 @@ B200_API int b200_bwd_uses_tensor_cores(int dtype, int d, int Nq, int Nkv);
 
 /* The same question for ONE CONCRETE CALL: which family b200_fa2_fwd(_ex) / b200_fa2_bwd(_ex) will run with these
  * pointers, shape, scale and flags.  Beyond (dtype, d) the tensor-core kernels need 16-byte aligned base pointers (TMA),
- * scale > 0 after the "0 means 1/sqrt(d)" rule (forward), and the fp32 backward is d = 64 non-causal only; a call that
+ * scale > 0 after the "0 means 1/sqrt(d)" rule (forward), and the fp32 backward is d = 64 only; a call that
  * misses one of these still runs, on the generic CUDA-core kernels (~15 TFLOP/s), and this is how a caller finds out.
  * Returns B200_ROUTE_TENSOR_CORE, B200_ROUTE_GENERIC or a negative b200_status for arguments the call would reject.
  * Pure host functions (no device needed); the calls themselves use exactly these predicates. */
@@ -132,8 +132,8 @@ B200_API int b200_fa2_fwd(const void* Q, const void* K, const void* V, void* O, 
  * B200_FLAG_CAUSAL: query row i attends to keys 0 .. i + (Nkv - Nq) only (bottom-right aligned, needs
  * Nkv >= Nq).  Not in the reference, which is non-causal; its own docs list it as the next step
  * (src/02_flash_attention_v2_backward/__info__/README.md:173).  d in {64,128} runs on the tensor-core kernels for any
- * Nq <= Nkv (masked diagonal tiles; tiles above the diagonal are skipped) -- except the fp32 backward, whose causal
- * form stays on the generic CUDA-core kernels like every other d.  flags = 0 is b200_fa2_fwd / b200_fa2_bwd. */
+ * Nq <= Nkv (masked diagonal tiles; tiles above the diagonal are skipped), the fp32 (tf32) backward at d = 64 included;
+ * every other d runs the generic CUDA-core kernels.  flags = 0 is b200_fa2_fwd / b200_fa2_bwd. */
 #define B200_FLAG_CAUSAL 1
 B200_API int b200_fa2_fwd_ex(const void* Q, const void* K, const void* V, void* O, float* L,
                     int B, int H, int Nq, int Nkv, int d, float scale, int dtype, int flags, cudaStream_t stream);

@@ -116,7 +116,7 @@ def test_descriptor_and_varlen_argument_checks_without_device():
 
 def test_route_query_reports_the_demotions():
     """b200_fa2_fwd_route / b200_fa2_bwd_route tell a caller which kernel family ONE call runs on, including the demotions
-    b200_*_uses_tensor_cores cannot see: unaligned pointers, scale <= 0, fp32 causal backward (pure host functions)."""
+    b200_*_uses_tensor_cores cannot see: unaligned pointers, scale <= 0, fp32 backward at d = 128 (pure host functions)."""
     R = fa.lib.b200_fa2_fwd_route
     BF, F32 = 0, 1
     A = 4096                                   # a 16-byte aligned dummy address (never dereferenced)
@@ -132,5 +132,6 @@ def test_route_query_reports_the_demotions():
     assert Rb(A, A, A, A, A, A, A, 8192, 8192, 128, 0.0, BF, 0) == 1
     assert Rb(A, A, A, A, A, A, A + 4, 8192, 8192, 128, 0.0, BF, 0) == 0
     assert Rb(A, A, A, A, A, A, A, 512, 1024, 128, 0.0, BF, 1) == 1
-    assert Rb(A, A, A, A, A, A, A, 512, 1024, 64, 0.0, F32, 1) == 0         # fp32 causal backward: generic
+    assert Rb(A, A, A, A, A, A, A, 512, 1024, 64, 0.0, F32, 1) == 1         # fp32 causal backward, d = 64: tf32 tensor cores (r2h)
+    assert Rb(A, A, A, A, A, A, A, 512, 1024, 128, 0.0, F32, 1) == 0        # fp32 d = 128 backward: generic
     assert Rb(A, A, A, A, A, A, A, 128, 128, 64, 0.0, F32, 0) == fa.lib.b200_bwd_uses_tensor_cores(F32, 64, 128, 128)

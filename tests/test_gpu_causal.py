@@ -48,7 +48,7 @@ def test_causal_forward_tensor_core(dtype, d, N):
 ])
 def test_causal_generic_and_bottom_right_alignment(dtype, d, Nq, Nkv):
     # Nq < Nkv: query i sees keys 0 .. i + (Nkv - Nq) (bottom-right aligned).  d in {64, 128}: tensor-core kernels (fp32:
-    # tf32 forward, generic backward); other d: the CUDA-core kernels
+    # tf32 forward; tf32 backward at d = 64, generic backward at d = 128); other d: the CUDA-core kernels
     rng = np.random.default_rng(Nq * 3 + Nkv)
     q = _rand((Nq, d), rng, dtype)
     k, v = _rand((Nkv, d), rng, dtype), _rand((Nkv, d), rng, dtype)
