@@ -16,6 +16,7 @@ _LIB = os.path.join(_HERE, "libnaive_oracle.so")
 _REF = os.path.join(_HERE, "_ref", "libref_naive.so")
 _REF_CUDA_FWD = os.path.join(_HERE, "_ref", "libref_cuda_fwd.so")
 _REF_CUDA_BWD = os.path.join(_HERE, "_ref", "libref_cuda_bwd.so")
+_REF_CUDA_RING = os.path.join(_HERE, "_ref", "libref_cuda_ring.so")
 
 _fp = C.POINTER(C.c_float)
 _dp = C.POINTER(C.c_double)
@@ -28,7 +29,8 @@ def build(force=False):
         subprocess.check_call(["make", "-C", _HERE, "libnaive_oracle.so"], stdout=subprocess.DEVNULL)
     if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF)):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
-    if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF_CUDA_FWD) or not os.path.exists(_REF_CUDA_BWD)):
+    if os.path.isdir("/root/reference/src") and (force or not os.path.exists(_REF_CUDA_FWD) or not os.path.exists(_REF_CUDA_BWD)
+                                               or not os.path.exists(_REF_CUDA_RING)):
         import shutil
         if shutil.which("nvcc"):
             subprocess.check_call(["make", "-C", _HERE, "refcuda"], stdout=subprocess.DEVNULL)
@@ -261,3 +263,28 @@ def ref_cuda_backward(Q, K, V, O, L, dO, dQ, dK, dV, scale):
     vp = C.c_void_p
     return int(_ref_cuda_lib("bwd").ref_cuda_fa2_backward(*[vp(t.data_ptr()) for t in (Q, K, V, O, L, dO, dQ, dK, dV)],
                                                           C.c_int(N), C.c_int(d), C.c_float(scale)))
+
+
+def ref_cuda_ring_available():
+    return os.path.exists(_REF_CUDA_RING)
+
+
+def ref_cuda_ring_forward(Q, K, V, P, scale):
+    """The reference's ring_attention_forward_kernel (src/03_flash_attention_v2_ring/common/ring_attention_kernel.cu:13-140)
+    run for the P ranks of a ring one after the other on one GPU, with the schedule and launch configuration of its host
+    loop (:159-214); torch CUDA float32 tensors [N, d], N % P == 0, d <= 64.  -> (O [N, d], L [N])."""
+    import torch
+    N, d = Q.shape
+    if "ring" not in _ref_cuda:
+        _ref_cuda["ring"] = C.CDLL(_REF_CUDA_RING)
+    O = torch.empty_like(Q)
+    L = torch.empty(N + 64, dtype=torch.float32, device=Q.device)
+    M = torch.empty(N + 64, dtype=torch.float32, device=Q.device)
+    torch.cuda.synchronize()
+    vp = C.c_void_p
+    rc = int(_ref_cuda["ring"].ref_cuda_ring_forward_emulated(vp(Q.data_ptr()), vp(K.data_ptr()), vp(V.data_ptr()), vp(O.data_ptr()),
+                                                              vp(L.data_ptr()), vp(M.data_ptr()), C.c_int(N), C.c_int(d), C.c_int(P),
+                                                              C.c_float(scale)))
+    if rc != 0:
+        raise RuntimeError(f"ref_cuda_ring_forward_emulated: {rc}")
+    return O, L[:N]
