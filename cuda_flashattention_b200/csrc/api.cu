@@ -181,10 +181,24 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
     }
     const size_t es = dtype == B200_DTYPE_F32 ? 4 : 2;
     const size_t slab = (size_t)N * d * es, lslab = (size_t)N * sizeof(float);
-    // chunk = as many (b,h) slabs as give ~32 MB per tensor: small enough to pipeline, large enough to fill the GPU
-    static size_t chunk_bytes = 0;                 // tuning hook: B200_HOST_CHUNK_MB
-    if (!chunk_bytes) { const char* e = getenv("B200_HOST_CHUNK_MB"); chunk_bytes = (size_t)(e && atoi(e) > 0 ? atoi(e) : 32) << 20; }
+    // chunk = as many (b,h) slabs as make ONE WAVE of forward CTAs (256 query rows each), between 4 and 32 MB per tensor:
+    // the call is PCIe-bound, so what counts is how soon the first copy-out starts and how late the last copy-in ends
+    // (C3, r2h: 4 heads = 8 MB chunks 22.8 ms per pipelined step / 23.4 ms for one call alone; 16 heads = 32 MB: 23.5 / 26.4).
+    // The ring call (min_chunks > 1: every chunk is a whole ring pass) keeps the 32 MB rule.
+    static size_t chunk_bytes = 0;                 // tuning hook: B200_HOST_CHUNK_MB fixes the chunk size
+    static bool chunk_fixed = false;
+    if (!chunk_bytes) {
+        const char* e = getenv("B200_HOST_CHUNK_MB");
+        chunk_fixed = e && atoi(e) > 0;
+        chunk_bytes = (size_t)(chunk_fixed ? atoi(e) : 32) << 20;
+    }
     int hc = (int)(chunk_bytes / slab);
+    if (!chunk_fixed && min_chunks <= 1) {
+        const int ctas_per_head = (N + 255) / 256;
+        const int h_wave = num_sms() / ctas_per_head, h_min = (int)((((size_t)4 << 20) + slab - 1) / slab);
+        if (h_wave < hc) hc = h_wave;
+        if (hc < h_min) hc = h_min;
+    }
     if (min_chunks > 1 && hc > (BH + min_chunks - 1) / min_chunks) hc = (BH + min_chunks - 1) / min_chunks;
     if (hc < 1) hc = 1;
     if (hc > BH) hc = BH;
