@@ -246,6 +246,54 @@ static int host_pipeline(const void* hQ, const void* hK, const void* hV, const v
     return B200_OK;
 }
 
+// ---- side streams of the packed variable-length calls -------------------------------------------------
+// The sequences of a packed batch are independent launches; on ONE stream a batch of short sequences leaves most SMs idle
+// (a 512-token sequence of 16 heads is 32 forward CTAs).  They are spread round-robin over kVarlenStreams internal streams
+// that fork from and join back into the caller's stream with events, so the call stays stream-ordered for the caller.
+#ifndef B200_VARLEN_STREAMS
+#define B200_VARLEN_STREAMS 4                    // (a side build with 1 is the single-stream behaviour, for A/B timing)
+#endif
+constexpr int kVarlenStreams = B200_VARLEN_STREAMS;
+struct VarlenStreams {
+    cudaStream_t s[kVarlenStreams] = {};
+    cudaEvent_t fork = nullptr, join[kVarlenStreams] = {};
+    bool ready = false;
+};
+static VarlenStreams g_vs[64];
+static std::mutex g_vs_mu;                       // held while a call enqueues: the events are shared by the device's calls
+
+static int varlen_streams(VarlenStreams** out)
+{
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return B200_ERR_INVALID_ARGUMENT;
+    VarlenStreams& v = g_vs[dev];
+    if (!v.ready) {                              // (a failed creation is retried by the next call)
+        if (!v.fork) B200_CUDA_TRY(cudaEventCreateWithFlags(&v.fork, cudaEventDisableTiming));
+        for (int k = 0; k < kVarlenStreams; ++k) {
+            if (!v.s[k]) B200_CUDA_TRY(cudaStreamCreateWithFlags(&v.s[k], cudaStreamNonBlocking));
+            if (!v.join[k]) B200_CUDA_TRY(cudaEventCreateWithFlags(&v.join[k], cudaEventDisableTiming));
+        }
+        v.ready = true;
+    }
+    *out = &v;
+    return B200_OK;
+}
+static int varlen_fork(VarlenStreams* v, int used, cudaStream_t st)
+{
+    B200_CUDA_TRY(cudaEventRecord(v->fork, st));
+    for (int k = 0; k < used; ++k) B200_CUDA_TRY(cudaStreamWaitEvent(v->s[k], v->fork, 0));
+    return B200_OK;
+}
+static int varlen_join(VarlenStreams* v, int used, cudaStream_t st)
+{
+    for (int k = 0; k < used; ++k) {
+        B200_CUDA_TRY(cudaEventRecord(v->join[k], v->s[k]));
+        B200_CUDA_TRY(cudaStreamWaitEvent(st, v->join[k], 0));
+    }
+    return B200_OK;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -479,15 +527,23 @@ int b200_fa2_fwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
     const Lay lq = packed_lay(p->q, p->H, p->d), lk = packed_lay(p->k, p->Hkv, p->d), lv = packed_lay(p->v, p->Hkv, p->d),
               lo = packed_lay(p->o, p->H, p->d);
     const long long total_q = cu_q[n_seqs];
-    for (int i = 0; i < n_seqs; ++i) {
+    int n_active = 0;
+    for (int i = 0; i < n_seqs; ++i) n_active += cu_q[i + 1] > cu_q[i];
+    const int used = n_active < kVarlenStreams ? n_active : kVarlenStreams;      // 1: no side streams
+    std::unique_lock<std::mutex> vs_lock(g_vs_mu, std::defer_lock);
+    VarlenStreams* vs = nullptr;
+    if (used > 1) { vs_lock.lock(); B200_TRY(varlen_streams(&vs)); B200_TRY(varlen_fork(vs, used, st)); }
+    for (int i = 0, j = 0; i < n_seqs; ++i) {
         const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
         if (nq == 0) continue;
+        const cudaStream_t si = used > 1 ? vs->s[j++ % used] : st;
         FwdArgs a{(const uint8_t*)Q + (size_t)cu_q[i] * lq.sn * es, (const uint8_t*)K + (size_t)cu_k[i] * lk.sn * es,
                   (const uint8_t*)V + (size_t)cu_k[i] * lv.sn * es, (uint8_t*)O + (size_t)cu_q[i] * lo.sn * es, L + cu_q[i],
                   lq, lk, lv, lo, total_q, 1, p->H, p->Hkv, nq, nk, p->d, resolve_scale(p->scale, p->d), p->dtype,
                   (p->flags & B200_FLAG_CAUSAL) != 0};
-        B200_TRY(tc_fwd_strided(a, st));
+        B200_TRY(tc_fwd_strided(a, si));
     }
+    if (used > 1) B200_TRY(varlen_join(vs, used, st));
     return B200_OK;
 }
 
@@ -506,26 +562,36 @@ int b200_fa2_bwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
     const Lay lq = packed_lay(p->q, H, d), lk = packed_lay(p->k, p->Hkv, d), lv = packed_lay(p->v, p->Hkv, d),
               lo = packed_lay(p->o, H, d), ldo = packed_lay(p->d_o, H, d), ldq = packed_lay(p->dq, H, d),
               ldk = packed_lay(p->dk, p->Hkv, d), ldv = packed_lay(p->dv, p->Hkv, d);
-    // one workspace, sized for the longest sequence; the sequences run back to back on the stream
-    void* ws;
-    const size_t need = bwd_ws_bytes(H, mq, mk, d, p->dtype);
-    B200_TRY(arena_get(need, &ws));
+    // one workspace per side stream, each sized for the longest sequence; a stream's sequences run back to back on it
+    int n_active = 0;
+    for (int i = 0; i < n_seqs; ++i) n_active += cu_q[i + 1] > cu_q[i];
+    const int used = n_active < kVarlenStreams ? n_active : kVarlenStreams;
+    void* ws0;
+    const size_t need = (bwd_ws_bytes(H, mq, mk, d, p->dtype) + 255) & ~(size_t)255;
+    B200_TRY(arena_get(need * (size_t)(used > 1 ? used : 1), &ws0));
+    std::unique_lock<std::mutex> vs_lock(g_vs_mu, std::defer_lock);
+    VarlenStreams* vs = nullptr;
+    if (used > 1) { vs_lock.lock(); B200_TRY(varlen_streams(&vs)); B200_TRY(varlen_fork(vs, used, st)); }
     const long long total_q = cu_q[n_seqs];
-    for (int i = 0; i < n_seqs; ++i) {
+    for (int i = 0, j = 0; i < n_seqs; ++i) {
         const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
         if (nq == 0) continue;
+        const int slot = used > 1 ? j++ % used : 0;
+        const cudaStream_t si = used > 1 ? vs->s[slot] : st;
+        uint8_t* ws = reinterpret_cast<uint8_t*>(ws0) + (size_t)slot * need;
         const size_t q0 = (size_t)cu_q[i], k0 = (size_t)cu_k[i];
         float* D = reinterpret_cast<float*>(ws);
         const size_t dbytes = (((size_t)H * nq * sizeof(float)) + 255) & ~(size_t)255;
         const void* dOi = (const uint8_t*)dO + q0 * ldo.sn * es;
         const void* Oi = (const uint8_t*)O + q0 * lo.sn * es;
-        B200_TRY(rowdot_strided(dOi, Oi, ldo, lo, D, 1, H, nq, d, p->dtype, st));
+        B200_TRY(rowdot_strided(dOi, Oi, ldo, lo, D, 1, H, nq, d, p->dtype, si));
         BwdArgs a{(const uint8_t*)Q + q0 * lq.sn * es, (const uint8_t*)K + k0 * lk.sn * es, (const uint8_t*)V + k0 * lv.sn * es, dOi,
                   L + q0, D, (uint8_t*)dQ + q0 * ldq.sn * es, (uint8_t*)dK + k0 * ldk.sn * es, (uint8_t*)dV + k0 * ldv.sn * es,
                   lq, lk, lv, ldo, ldq, ldk, ldv, 1, H, p->Hkv, nq, nk, d, resolve_scale(p->scale, d), p->dtype,
                   (p->flags & B200_FLAG_CAUSAL) != 0, total_q};
-        B200_TRY(tc_bwd_strided(a, reinterpret_cast<uint8_t*>(ws) + dbytes, need - dbytes, st));
+        B200_TRY(tc_bwd_strided(a, ws + dbytes, need - dbytes, si));
     }
+    if (used > 1) B200_TRY(varlen_join(vs, used, st));
     return B200_OK;
 }
 

@@ -165,8 +165,9 @@ B200_API int b200_fa2_bwd_desc(const b200_attn_desc* desc, const void* Q, const 
  * Q/O/dO/dQ are [total_q, H, d], K/V/dK/dV [total_k, Hkv, d] (head / row strides from the descriptor's layouts, all
  * zero = contiguous; batch strides, B, Nq, Nkv are ignored); sequence i is rows cu_seqlens[i] .. cu_seqlens[i+1]-1
  * (HOST arrays of n_seqs + 1 ints).  L is [H, total_q] fp32.  One launch sequence per batch entry on the tensor-core
- * kernels (d in {64,128}; backward bf16; causal needs equal q / k lengths); the backward takes its scratch from the
- * library's arena. */
+ * kernels (d in {64,128}; backward bf16; causal needs q length <= k length per sequence, bottom-right aligned); the
+ * sequences are independent launches and are spread over a few internal streams that fork from and join back into
+ * `stream` (the call stays stream-ordered for the caller); the backward takes its scratch from the library's arena. */
 B200_API int b200_fa2_fwd_varlen(const b200_attn_desc* desc, int n_seqs, const int* cu_seqlens_q, const int* cu_seqlens_k,
                         const void* Q, const void* K, const void* V, void* O, float* L, cudaStream_t stream);
 B200_API int b200_fa2_bwd_varlen(const b200_attn_desc* desc, int n_seqs, const int* cu_seqlens_q, const int* cu_seqlens_k,

@@ -187,3 +187,33 @@ def test_packed_variable_length_batch(causal, Hkv):
                 dV_ref = rv if dV_ref is None else dV_ref + rv
             assert rel_l2(host(dK[sk, hk]), dK_ref) <= 1e-2 and rel_l2(host(dV[sk, hk]), dV_ref) <= 1e-2
             assert np.abs(host(dV[sk, hk]) - dV_ref).max() <= 2e-2 * max(1.0, float(np.abs(dV_ref).max()))
+
+
+def test_packed_variable_length_batch_more_sequences_than_side_streams():
+    # r2h: the sequences of a packed batch run on 4 internal streams (round-robin), each with its own workspace slot; nine
+    # sequences (one of them empty) make every stream and slot serve two or three of them, in both directions
+    H, Hkv, d = 4, 2, 128
+    lens = [130, 64, 0, 257, 96, 333, 64, 200, 150]
+    cu = np.concatenate([[0], np.cumsum(lens)])
+    q, do = _rand((cu[-1], H, d), 11), _rand((cu[-1], H, d), 12)
+    k, v = _rand((cu[-1], Hkv, d), 13), _rand((cu[-1], Hkv, d), 14)
+    O, L = fa.attention_varlen_forward(q, k, v, cu, cu, causal=True)
+    dQ, dK, dV = fa.attention_varlen_backward(q, k, v, O, L, do, cu, cu, causal=True)
+    torch.cuda.synchronize()
+    G = H // Hkv
+    for i in range(len(lens)):
+        if lens[i] == 0:
+            continue
+        s = slice(cu[i], cu[i + 1])
+        for hk in range(Hkv):
+            dK_ref = dV_ref = None
+            for g in range(G):
+                h = hk * G + g
+                args = (host(q[s, h]), host(k[s, hk]), host(v[s, hk]))
+                Oo, Lo = oracle.forward(*args, 0.0, causal=True)
+                assert np.abs(host(O[s, h]) - Oo).max() <= 2e-2 * max(1.0, float(np.abs(Oo).max())) and np.abs(host(L[h, s]) - Lo).max() <= 2e-2
+                rq, rk, rv = oracle.backward(*args, host(do[s, h]), 0.0, causal=True)
+                assert rel_l2(host(dQ[s, h]), rq) <= 1e-2, (i, h)
+                dK_ref = rk if dK_ref is None else dK_ref + rk
+                dV_ref = rv if dV_ref is None else dV_ref + rv
+            assert rel_l2(host(dK[s, hk]), dK_ref) <= 1e-2 and rel_l2(host(dV[s, hk]), dV_ref) <= 1e-2, (i, hk)
