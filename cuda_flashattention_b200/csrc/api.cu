@@ -533,6 +533,7 @@ int b200_fa2_fwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
     std::unique_lock<std::mutex> vs_lock(g_vs_mu, std::defer_lock);
     VarlenStreams* vs = nullptr;
     if (used > 1) { vs_lock.lock(); B200_TRY(varlen_streams(&vs)); B200_TRY(varlen_fork(vs, used, st)); }
+    int rc = B200_OK;
     for (int i = 0, j = 0; i < n_seqs; ++i) {
         const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
         if (nq == 0) continue;
@@ -541,10 +542,12 @@ int b200_fa2_fwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
                   (const uint8_t*)V + (size_t)cu_k[i] * lv.sn * es, (uint8_t*)O + (size_t)cu_q[i] * lo.sn * es, L + cu_q[i],
                   lq, lk, lv, lo, total_q, 1, p->H, p->Hkv, nq, nk, p->d, resolve_scale(p->scale, p->d), p->dtype,
                   (p->flags & B200_FLAG_CAUSAL) != 0};
-        B200_TRY(tc_fwd_strided(a, si));
+        rc = tc_fwd_strided(a, si);
+        if (rc != B200_OK) break;
     }
-    if (used > 1) B200_TRY(varlen_join(vs, used, st));
-    return B200_OK;
+    // (joined also after a failed launch: whatever was enqueued on the side streams stays ordered before the caller's next work)
+    if (used > 1) { const int jr = varlen_join(vs, used, st); if (rc == B200_OK) rc = jr; }
+    return rc;
 }
 
 int b200_fa2_bwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, const int* cu_k, const void* Q, const void* K,
@@ -573,6 +576,7 @@ int b200_fa2_bwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
     VarlenStreams* vs = nullptr;
     if (used > 1) { vs_lock.lock(); B200_TRY(varlen_streams(&vs)); B200_TRY(varlen_fork(vs, used, st)); }
     const long long total_q = cu_q[n_seqs];
+    int rc = B200_OK;
     for (int i = 0, j = 0; i < n_seqs; ++i) {
         const int nq = cu_q[i + 1] - cu_q[i], nk = cu_k[i + 1] - cu_k[i];
         if (nq == 0) continue;
@@ -584,15 +588,17 @@ int b200_fa2_bwd_varlen(const b200_attn_desc* p, int n_seqs, const int* cu_q, co
         const size_t dbytes = (((size_t)H * nq * sizeof(float)) + 255) & ~(size_t)255;
         const void* dOi = (const uint8_t*)dO + q0 * ldo.sn * es;
         const void* Oi = (const uint8_t*)O + q0 * lo.sn * es;
-        B200_TRY(rowdot_strided(dOi, Oi, ldo, lo, D, 1, H, nq, d, p->dtype, si));
+        rc = rowdot_strided(dOi, Oi, ldo, lo, D, 1, H, nq, d, p->dtype, si);
+        if (rc != B200_OK) break;
         BwdArgs a{(const uint8_t*)Q + q0 * lq.sn * es, (const uint8_t*)K + k0 * lk.sn * es, (const uint8_t*)V + k0 * lv.sn * es, dOi,
                   L + q0, D, (uint8_t*)dQ + q0 * ldq.sn * es, (uint8_t*)dK + k0 * ldk.sn * es, (uint8_t*)dV + k0 * ldv.sn * es,
                   lq, lk, lv, ldo, ldq, ldk, ldv, 1, H, p->Hkv, nq, nk, d, resolve_scale(p->scale, d), p->dtype,
                   (p->flags & B200_FLAG_CAUSAL) != 0, total_q};
-        B200_TRY(tc_bwd_strided(a, ws + dbytes, need - dbytes, si));
+        rc = tc_bwd_strided(a, ws + dbytes, need - dbytes, si);
+        if (rc != B200_OK) break;
     }
-    if (used > 1) B200_TRY(varlen_join(vs, used, st));
-    return B200_OK;
+    if (used > 1) { const int jr = varlen_join(vs, used, st); if (rc == B200_OK) rc = jr; }
+    return rc;
 }
 
 size_t b200_fa2_bwd_workspace_bytes(int B, int H, int Nq, int Nkv, int d, int dtype)
